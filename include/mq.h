@@ -1,0 +1,150 @@
+/*
+ * mq.h -- C ABI of libmq.so: the B200 (sm_100a) implementation of the W4A4 MixedQuant linear hot path.
+ *
+ * The reference (adithyab100/smoothquant-mixedprecision) is pure PyTorch and has no FFI; the "binding" a
+ * maintainer adds is a ctypes stub.  Each entry point below names the reference code it
+ * replaces, relative to /root/reference.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless the name ends in _host; sizes are element counts unless named
+ *     *_bytes; `ld*` are leading dimensions in ELEMENTS of the pointed-to type
+ *   - every call is asynchronous on `stream` (a cudaStream_t passed as void*), never synchronises, never
+ *     allocates device memory, never throws, never exits the process
+ *   - return value: 0 on success, a negative MQ_ERR_* otherwise; mq_last_error() gives a thread-local message
+ *   - dtype codes: MQ_F16 / MQ_BF16 / MQ_F32 (the dtype the reference tensor lives in; all arithmetic is rounded
+ *     to that dtype exactly like the reference's in-place torch ops)
+ *   - there is no CPU fallback: without a CUDA device every compute call returns MQ_ERR_CUDA
+ */
+#ifndef MQ_H_
+#define MQ_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MQ_ABI_VERSION 1
+
+enum { MQ_F16 = 0, MQ_BF16 = 1, MQ_F32 = 2 };
+
+enum {
+  MQ_OK = 0,
+  MQ_ERR_ARG = -1,        /* invalid argument (shape, alignment, dtype, null pointer)                     */
+  MQ_ERR_CUDA = -2,       /* CUDA runtime / driver error, or no device                                      */
+  MQ_ERR_UNSUPPORTED = -3,/* combination not implemented by this build (message says which)                 */
+  MQ_ERR_WORKSPACE = -4   /* workspace too small                                                            */
+};
+
+/* column statistic kinds for mq_colstat */
+enum {
+  MQ_STAT_ABSMAX = 0,     /* max_m |x_mk|                      fake_quant.py:113 / :164 ; calibration.py:18-25 */
+  MQ_STAT_ABSMEAN = 1,    /* mean_m |x_mk|                     run_experiments.py:60 (importance)              */
+  MQ_STAT_MEAN3STD = 2,   /* mean + 3*std (unbiased) of |x|    README.md:36 -- parity unpinned                 */
+  MQ_STAT_ARGMAX = 3      /* first row index attaining max|x|  README.md:37 -- parity unpinned                 */
+};
+
+int         mq_version(void);
+const char* mq_last_error(void);
+/* sm_count / cc_major / cc_minor of the current device; any pointer may be NULL */
+int         mq_device_info(int* sm_count, int* cc_major, int* cc_minor);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * K0  column statistics over the rows of x [M, K] (row-major, leading dimension ld).
+ *     Replaces  t.abs().max(dim=0).values            fake_quant.py:113 (activations), :164 (weights)
+ *               x.view(-1,K).abs().mean(dim=0)       run_experiments.py:60
+ *     out_key: float32 [K].  workspace: mq_colstat_workspace_bytes(K, kind) bytes.
+ * ---------------------------------------------------------------------------------------------------------- */
+size_t mq_colstat_workspace_bytes(int64_t K, int kind);
+int mq_colstat(const void* x, int64_t M, int64_t K, int64_t ld, int dtype, int kind,
+               float* out_key, void* workspace, size_t workspace_bytes, void* stream);
+
+/* K0b stable ascending argsort of n float32 keys (ties -> ascending index; the canonical order of SURVEY F3).
+ *     Replaces  torch.argsort(col_max_val)           fake_quant.py:116, :167
+ *     With descending != 0: descending keys, ties still by ascending index  (fake_quant.py:268).
+ *     `subset` (nullable, int32 [n]) : sort only these column ids, keyed by key[subset[i]]; the output then
+ *     holds column ids (used to sort the non-salient columns, fake_quant.py:293-300).
+ *     out_perm: int32 [n].  workspace: mq_argsort_workspace_bytes(n). */
+size_t mq_argsort_workspace_bytes(int64_t n);
+int mq_argsort_stable(const float* key, const int32_t* subset, int64_t n, int descending, int32_t* out_perm,
+                      void* workspace, size_t workspace_bytes, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * K1 / P0  fused row quantiser (activations: rows = tokens; weights: rows = output channels).
+ *     For every row r:  v_j = x[r, perm[j]] (optionally / smooth[perm[j]]),  j in [0, Kn)
+ *                       groups of `group_size` consecutive j (last one zero-padded),
+ *                       scale = clamp(absmax, 1e-5) / qmax,  code = round_half_even(v / scale)     (dtype-rounded)
+ *     Replaces  quantize_activation_per_group_absmax   fake_quant.py:78-101  applied to x[:, perm]
+ *               quantize_weight_per_group_absmax       fake_quant.py:30-53   applied to W[:, perm]
+ *               the boolean-mask salient split         fake_quant.py:291-298, :347
+ *     Outputs   codes  int8  [R, ld_codes]   codes in [-qmax, qmax]; columns [Kn, ld_codes) are written as 0
+ *               scales float [G, ld_scales]  TRANSPOSED (group-major) and widened to fp32: scales[g*ld + r]
+ *               sal    dtype [R, ld_sal]     x[r, sal[j]] for j < Ks, zeros in [Ks, ld_sal)  (nullable if Ks==0)
+ *     perm: int32 [Kn] original column of permuted position j; sal: int32 [Ks]; smooth: dtype [K] or NULL.
+ *     Constraints: K <= 65535; ld_codes >= G*group_size (the GEMM wants it rounded up to 128); ld_scales >= R.
+ * ---------------------------------------------------------------------------------------------------------- */
+int mq_quant_rows(const void* x, int64_t R, int64_t K, int64_t ld, int dtype, const void* smooth,
+                  const int32_t* perm, int64_t Kn, const int32_t* sal, int64_t Ks,
+                  int group_size, int n_bits,
+                  int8_t* out_codes, int64_t ld_codes, float* out_scales, int64_t ld_scales,
+                  void* out_sal, int64_t ld_sal, void* stream);
+
+/* Same arithmetic, reference-shaped output: out [R, K] (dtype) holds code*scale at the ORIGINAL column of every
+ * permuted position and x itself at every column not listed in perm (salient pass-through).
+ *     Replaces  quantize_activation_per_group_absmax_sort   fake_quant.py:105-154  (perm = argsort of the key)
+ *               quantize_weight_per_group_absmax_sort       fake_quant.py:157-207
+ *               per-token / per-channel quantisers          fake_quant.py:57-64, :10-16 (group_size = Kn, identity perm)
+ *               the scatter-back                            fake_quant.py:301, :363-365
+ *     `out` may alias `x` (in-place, like the reference's per_token path). */
+int mq_fakequant_rows(const void* x, int64_t R, int64_t K, int64_t ld, int dtype,
+                      const int32_t* perm, int64_t Kn, int group_size, int n_bits,
+                      void* out, int64_t ld_out, void* stream);
+
+/* per-tensor fake quantiser (one global scale): fake_quant.py:68-75, :20-26.  workspace >= 16 bytes. */
+int mq_fakequant_tensor(const void* x, int64_t n, int dtype, int n_bits, void* out,
+                        void* workspace, size_t workspace_bytes, void* stream);
+
+/* int4 storage format of the weight packer: two's-complement nibbles, even column in the low nibble.
+ * codes [R, ld_codes] int8  <->  packed [R, ld_packed] uint8 (cols/2 bytes used per row). */
+int mq_pack_int4(const int8_t* codes, int64_t R, int64_t cols, int64_t ld_codes,
+                 uint8_t* packed, int64_t ld_packed, void* stream);
+int mq_unpack_int4(const uint8_t* packed, int64_t R, int64_t cols, int64_t ld_packed,
+                   int8_t* codes, int64_t ld_codes, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * K2  fused mixed-precision GEMM  (tcgen05 kind::i8 per K-group + kind::f16 salient slice, one CTA, TMEM accum.)
+ *     y[m, n] = sum_g a_scales[g, m] * w_scales[g, n] * sum_{k in g} a_codes[m, k] * w_codes[n, k]
+ *             + sum_j a_sal[m, j] * w_sal[n, j]  + bias[n]
+ *     Replaces  torch.functional.F.linear(q_x, self.weight, self.bias)     fake_quant.py:306
+ *     a_codes [M, lda] int8, w_codes [N, ldw] int8    (K-major, G*group_size valid columns, zero padded to 128)
+ *     a_scales [G, ld_as] fp32, w_scales [G, ld_ws] fp32 (group-major, as written by mq_quant_rows)
+ *     a_sal [M, ld_asal], w_sal [N, ld_wsal] in `dtype` (MQ_F16 or MQ_BF16), Ks valid columns (any count; the
+ *           kernel walks them in blocks of 64 and TMA zero-fills the tail), ld % 8 == 0, 16-byte aligned
+ *     bias [N] in `dtype` or NULL;  y [M, ldy] in `dtype`.
+ *     G == 0 runs the pure 16-bit GEMM (mode="reference": dequantised operands in a_sal / w_sal);
+ *     Ks == 0 runs the pure integer path.  group_size must be 32, 64 or a multiple of 128.
+ * ---------------------------------------------------------------------------------------------------------- */
+size_t mq_mixed_gemm_workspace_bytes(int64_t M, int64_t N);
+int mq_mixed_gemm(const int8_t* a_codes, int64_t lda, const float* a_scales, int64_t ld_as,
+                  const void* a_sal, int64_t ld_asal,
+                  const int8_t* w_codes, int64_t ldw, const float* w_scales, int64_t ld_ws,
+                  const void* w_sal, int64_t ld_wsal,
+                  const void* bias, int64_t M, int64_t N, int64_t G, int group_size, int64_t Ks,
+                  int dtype, void* y, int64_t ldy,
+                  void* workspace, size_t workspace_bytes, void* stream);
+
+/* tuning knobs (process-global, for benchmarks/tests): name in {"gemm_bn", "gemm_stages", "quant_rows_per_stage",
+ * "quant_warps", "quant_force_generic", ...}; value 0 restores the default.  MQ_ERR_ARG for unknown names. */
+int mq_set_option(const char* name, int value);
+
+/* debug: every in-kernel barrier wait is bounded (2 s); one that expires records {code, block, thread, parity,
+ * spins>>10, 0, 0, 0} instead of hanging the GPU.  These copy the record of the quantiser / GEMM kernels to
+ * out8_host (8 x uint32, HOST pointer) and clear it.  code == 0 means no fault.  They synchronise the device. */
+int mq_quant_fault(unsigned int* out8_host);
+int mq_gemm_fault(unsigned int* out8_host);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MQ_H_ */

@@ -1,0 +1,397 @@
+// K2: fused mixed-precision GEMM for the W4A4 MixedQuant linear layer (sm_100a: TMA + tcgen05 + TMEM).
+//
+//   y[m, n] = sum_g a_scale[g, m] * w_scale[g, n] * sum_{k in group g} a_code[m, k] * w_code[n, k]     (kind::i8)
+//           + sum_j a_sal[m, j] * w_sal[n, j]                                                           (kind::f16)
+//           + bias[n]
+//
+// Replaces  torch.functional.F.linear(q_x, self.weight, self.bias)   /root/reference/smoothquant/fake_quant.py:306
+// where q_x / self.weight hold dequantised code*scale values in the non-salient columns and FP16 originals in the
+// salient ones (fake_quant.py:291-301, :347-365).
+//
+// One CTA computes a 128 x BN tile of y.  Warp roles:
+//   warp 0      TMA producer: 128-byte-wide K blocks of A (128 rows) and W (BN rows) into a kStages ring
+//               (SWIZZLE_128B, one mbarrier pair per stage)
+//   warp 1      MMA issuer (one thread): per K group g it issues g/32 tcgen05.mma.kind::i8 (M=128, N=BN, K=32)
+//               into one of two TMEM accumulator stages (int32), commits the stage to the epilogue, moves on to
+//               the other stage; the salient slice is the last "group", issued as kind::f16 (fp32 accumulator)
+//   warp 2      TMEM allocation / deallocation (2*BN columns)
+//   warps 4..   epilogue: thread t of a warp owns TMEM lane (= tile row) 32*(warp%4)+t and CW columns; after each
+//               group it reads the int32 partial sums with tcgen05.ld, converts, multiplies by
+//               a_scale[g,m]*w_scale[g,n] and accumulates in fp32 registers, releases the TMEM stage, and at the
+//               end adds the bias, rounds to fp16/bf16 and stores the row segment.
+#include <cuda.h>
+
+#include "common.cuh"
+#include "ptx.cuh"
+
+namespace {
+
+using namespace mqptx;
+
+constexpr int BM = 128;
+constexpr int kKBlockBytes = 128;  // one swizzle atom wide
+constexpr int kFirstEpiWarp = 4;
+
+struct GemmArgs {
+  const float* a_scales;
+  int64_t ld_as;
+  const float* w_scales;
+  int64_t ld_ws;
+  const void* bias;
+  void* y;
+  int64_t ldy;
+  int M, N, G, g;
+  int kb_int;  // 128-column K blocks of codes holding the G*g quantised columns
+  int kb_sal;  // 64-column K blocks of the salient slice
+};
+
+template <int BN, int kStages>
+struct SmemLayout {
+  static constexpr int kABytes = BM * kKBlockBytes;
+  static constexpr int kBBytes = BN * kKBlockBytes;
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kBarOffset = kStages * kStageBytes;
+  // full[kStages], empty[kStages], tmem_full[2], tmem_empty[2], tmem base (u32)
+  static constexpr int kBarBytes = (2 * kStages + 4) * 8 + 16;
+  static constexpr int kTotal = kBarOffset + kBarBytes + 1024;  // + slack to align the base to 1024 bytes
+};
+
+template <typename OutT, int BN, int CW, int kStages>
+__global__ void __launch_bounds__((kFirstEpiWarp + 4 * BN / CW) * 32, 1)
+mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_w,
+                  const __grid_constant__ CUtensorMap map_as, const __grid_constant__ CUtensorMap map_ws,
+                  const GemmArgs p) {
+  using L = SmemLayout<BN, kStages>;
+  constexpr int kEpiWarps = 4 * BN / CW;
+  constexpr int kTmemCols = 2 * BN;
+  static_assert(BN % CW == 0 && CW % 32 == 0, "bad epilogue split");
+  static_assert(kTmemCols == 256 || kTmemCols == 512 || kTmemCols == 128, "TMEM columns must be a power of two");
+
+  extern __shared__ unsigned char smem_raw[];
+  const uint32_t raw_addr = smem_u32(smem_raw);
+  unsigned char* smem = smem_raw + (((raw_addr + 1023u) & ~1023u) - raw_addr);
+
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + L::kBarOffset);
+  uint64_t* empty_bar = full_bar + kStages;
+  uint64_t* tfull_bar = empty_bar + kStages;
+  uint64_t* tempty_bar = tfull_bar + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n0 = blockIdx.x * BN, m0 = blockIdx.y * BM;
+  const int units = p.G + (p.kb_sal > 0 ? 1 : 0);  // accumulation units: K groups, then the salient slice
+  const int kb_total = p.kb_int + p.kb_sal;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&map_a);
+    tma_prefetch_desc(&map_w);
+    tma_prefetch_desc(&map_as);
+    tma_prefetch_desc(&map_ws);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < kStages; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    for (int t = 0; t < 2; ++t) {
+      mbar_init(&tfull_bar[t], 1);
+      mbar_init(&tempty_bar[t], kEpiWarps);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 2) tmem_alloc<kTmemCols>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(tmem_slot);
+
+  if (warp == 0) {
+    // ------------------------------------------------------------------ TMA producer
+    if (lane == 0) {
+      for (int kb = 0; kb < kb_total; ++kb) {
+        const int s = kb % kStages;
+        const uint32_t ph = (uint32_t)(kb / kStages) & 1u;
+        if (!mbar_wait(&empty_bar[s], ph ^ 1u, 0x200u + s)) break;
+        unsigned char* sa = smem + (size_t)s * L::kStageBytes;
+        unsigned char* sb = sa + L::kABytes;
+        mbar_expect_tx(&full_bar[s], (uint32_t)L::kStageBytes);
+        if (kb < p.kb_int) {
+          tma_load_2d(sa, &map_a, kb * 128, m0, &full_bar[s]);
+          tma_load_2d(sb, &map_w, kb * 128, n0, &full_bar[s]);
+        } else {
+          const int ks = (kb - p.kb_int) * 64;
+          tma_load_2d(sa, &map_as, ks, m0, &full_bar[s]);
+          tma_load_2d(sb, &map_ws, ks, n0, &full_bar[s]);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------------ MMA issuer
+    if (lane == 0) {
+      constexpr uint32_t idesc_i8 = umma_idesc(2u, 1u, BM, BN);
+      const uint32_t idesc_f16 = umma_idesc(1u, sizeof(OutT) == 2 && Num<OutT>::kDtype == MQ_BF16 ? 1u : 0u, BM, BN);
+      const int mma_per_group = p.g / 32;
+      int kb = 0;        // K block currently being consumed
+      int sub = 0;       // next 32-byte slice inside the K block (0..3)
+      bool ok = true;
+      for (int u = 0; u < units && ok; ++u) {
+        const int t = u & 1;
+        if (!mbar_wait(&tempty_bar[t], ((uint32_t)(u >> 1) & 1u) ^ 1u, 0x300u + t)) break;
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + (uint32_t)(t * BN);
+        const bool is_sal = u >= p.G;
+        if (is_sal && sub != 0) {  // codes end in the middle of a K block (zero padding): release it
+          tc_commit(&empty_bar[kb % kStages]);
+          ++kb;
+          sub = 0;
+        }
+        const int n_mma = is_sal ? p.kb_sal * 4 : mma_per_group;
+        for (int i = 0; i < n_mma; ++i) {
+          const int s = kb % kStages;
+          if (sub == 0) {
+            if (!mbar_wait(&full_bar[s], (uint32_t)(kb / kStages) & 1u, 0x400u + s)) {
+              ok = false;
+              break;
+            }
+            tc_fence_after();
+          }
+          const uint32_t sa = smem_u32(smem + (size_t)s * L::kStageBytes);
+          const uint64_t da = umma_desc_k128(sa) + (uint64_t)(sub * 2);
+          const uint64_t db = umma_desc_k128(sa + L::kABytes) + (uint64_t)(sub * 2);
+          if (is_sal)
+            mma_f16_ss(d_tmem, da, db, idesc_f16, i > 0 ? 1u : 0u);
+          else
+            mma_i8_ss(d_tmem, da, db, idesc_i8, i > 0 ? 1u : 0u);
+          if (++sub == 4) {
+            tc_commit(&empty_bar[s]);  // smem stage free once these MMAs have read it
+            ++kb;
+            sub = 0;
+          }
+        }
+        if (!ok) break;
+        tc_commit(&tfull_bar[t]);  // accumulator stage t complete -> epilogue
+      }
+    }
+  } else if (warp >= kFirstEpiWarp) {
+    // ------------------------------------------------------------------ epilogue
+    const int ew = warp - kFirstEpiWarp;
+    const int quarter = warp & 3;                  // TMEM lane quarter this warp may access
+    const int col0 = (ew / 4) * CW;                // first tile column owned by this thread
+    const int m = m0 + quarter * 32 + lane;
+    const bool row_ok = m < p.M;
+    float acc[CW];
+#pragma unroll
+    for (int j = 0; j < CW; ++j) acc[j] = 0.f;
+
+    bool ok = true;
+    for (int u = 0; u < units && ok; ++u) {
+      const int t = u & 1;
+      const bool is_sal = u >= p.G;
+      float as = 1.f;
+      if (!is_sal) as = row_ok ? __ldg(p.a_scales + (int64_t)u * p.ld_as + m) : 0.f;
+      const float* wsp = p.w_scales + (int64_t)u * p.ld_ws + n0 + col0;
+      if (!mbar_wait(&tfull_bar[t], (uint32_t)(u >> 1) & 1u, 0x500u + t)) {
+        ok = false;
+        break;
+      }
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(t * BN + col0);
+#pragma unroll
+      for (int c = 0; c < CW / 32; ++c) {
+        uint32_t v[32];
+        tmem_ld_32x32(taddr + (uint32_t)(c * 32), v);
+        tmem_ld_wait();
+        if (is_sal) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) acc[c * 32 + j] += __uint_as_float(v[j]);
+        } else {
+#pragma unroll
+          for (int j4 = 0; j4 < 8; ++j4) {
+            float4 ws = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (n0 + col0 + c * 32 + j4 * 4 < p.N) ws = __ldg(reinterpret_cast<const float4*>(wsp + c * 32 + j4 * 4));
+            acc[c * 32 + j4 * 4 + 0] = fmaf((float)(int)v[j4 * 4 + 0], as * ws.x, acc[c * 32 + j4 * 4 + 0]);
+            acc[c * 32 + j4 * 4 + 1] = fmaf((float)(int)v[j4 * 4 + 1], as * ws.y, acc[c * 32 + j4 * 4 + 1]);
+            acc[c * 32 + j4 * 4 + 2] = fmaf((float)(int)v[j4 * 4 + 2], as * ws.z, acc[c * 32 + j4 * 4 + 2]);
+            acc[c * 32 + j4 * 4 + 3] = fmaf((float)(int)v[j4 * 4 + 3], as * ws.w, acc[c * 32 + j4 * 4 + 3]);
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tempty_bar[t]);
+    }
+
+    if (ok && row_ok) {
+      OutT* yrow = static_cast<OutT*>(p.y) + (int64_t)m * p.ldy + n0 + col0;
+      const OutT* bias = static_cast<const OutT*>(p.bias);
+      const bool vec_ok = (p.ldy % 8 == 0) && (reinterpret_cast<uintptr_t>(p.y) % 16 == 0);
+#pragma unroll
+      for (int j8 = 0; j8 < CW / 8; ++j8) {
+        const int n = n0 + col0 + j8 * 8;
+        if (n >= p.N) break;
+        __align__(16) OutT o[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          float r = acc[j8 * 8 + e];
+          if (bias && n + e < p.N) r += Num<OutT>::to_f(bias[n + e]);
+          o[e] = Num<OutT>::from_f(r);
+        }
+        if (vec_ok && n + 8 <= p.N) {
+          *reinterpret_cast<uint4*>(yrow + j8 * 8) = *reinterpret_cast<const uint4*>(o);
+        } else {
+          for (int e = 0; e < 8 && n + e < p.N; ++e) yrow[j8 * 8 + e] = o[e];
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc<kTmemCols>(tmem_base);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ host side
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (fn) return fn;
+  void* p = nullptr;
+  cudaDriverEntryPointQueryResult q;
+  if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+      q != cudaDriverEntryPointSuccess || !p)
+    return nullptr;
+  fn = reinterpret_cast<EncodeTiledFn>(p);
+  return fn;
+}
+
+// 2-D row-major tensor [rows, cols] of `esize`-byte elements with leading dimension ld (elements); box = 128 bytes
+// of the inner dimension x box_rows rows, 128-byte swizzle.
+int make_map(CUtensorMap* map, const void* ptr, CUtensorMapDataType dt, int esize, int64_t rows, int64_t cols,
+             int64_t ld, int box_rows) {
+  EncodeTiledFn enc = get_encode_fn();
+  if (!enc) {
+    mq_set_error("cuTensorMapEncodeTiled entry point not available");
+    return MQ_ERR_CUDA;
+  }
+  cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)ld * (cuuint64_t)esize};
+  cuuint32_t box[2] = {(cuuint32_t)(128 / esize), (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(map, dt, 2, const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    mq_set_error("cuTensorMapEncodeTiled failed with CUresult %d (rows=%lld cols=%lld ld=%lld esize=%d)", (int)r,
+                 (long long)rows, (long long)cols, (long long)ld, esize);
+    return MQ_ERR_CUDA;
+  }
+  return MQ_OK;
+}
+
+template <typename OutT, int BN, int CW, int kStages>
+int launch_gemm(const CUtensorMap& ma, const CUtensorMap& mw, const CUtensorMap& mas, const CUtensorMap& mws,
+                const GemmArgs& p, cudaStream_t st) {
+  using L = SmemLayout<BN, kStages>;
+  auto kern = mixed_gemm_kernel<OutT, BN, CW, kStages>;
+  MQ_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal));
+  dim3 grid((unsigned)((p.N + BN - 1) / BN), (unsigned)((p.M + BM - 1) / BM));
+  dim3 block((kFirstEpiWarp + 4 * BN / CW) * 32);
+  kern<<<grid, block, L::kTotal, st>>>(ma, mw, mas, mws, p);
+  MQ_CHECK_CUDA(cudaGetLastError());
+  return MQ_OK;
+}
+
+template <typename OutT>
+int dispatch_gemm(const CUtensorMap& ma, const CUtensorMap& mw, const CUtensorMap& mas, const CUtensorMap& mws,
+                  const GemmArgs& p, int bn, cudaStream_t st) {
+  if (bn == 256) return launch_gemm<OutT, 256, 128, 4>(ma, mw, mas, mws, p, st);
+  return launch_gemm<OutT, 128, 64, 6>(ma, mw, mas, mws, p, st);
+}
+
+}  // namespace
+
+extern "C" {
+
+size_t mq_mixed_gemm_workspace_bytes(int64_t M, int64_t N) {
+  (void)M;
+  (void)N;
+  return 0;
+}
+
+int mq_mixed_gemm(const int8_t* a_codes, int64_t lda, const float* a_scales, int64_t ld_as, const void* a_sal,
+                  int64_t ld_asal, const int8_t* w_codes, int64_t ldw, const float* w_scales, int64_t ld_ws,
+                  const void* w_sal, int64_t ld_wsal, const void* bias, int64_t M, int64_t N, int64_t G,
+                  int group_size, int64_t Ks, int dtype, void* y, int64_t ldy, void* workspace,
+                  size_t workspace_bytes, void* stream) {
+  (void)workspace;
+  (void)workspace_bytes;
+  MQ_CHECK_ARG(y && M >= 0 && N >= 1 && ldy >= N, "mq_mixed_gemm: bad output (M=%lld N=%lld ldy=%lld)", (long long)M,
+               (long long)N, (long long)ldy);
+  MQ_CHECK_ARG(dtype == MQ_F16 || dtype == MQ_BF16, "mq_mixed_gemm: dtype must be MQ_F16 or MQ_BF16");
+  MQ_CHECK_ARG(G >= 0 && Ks >= 0 && (G > 0 || Ks > 0), "mq_mixed_gemm: empty contraction");
+  MQ_CHECK_ARG(M < (1ll << 31) && N < (1ll << 31), "mq_mixed_gemm: shape too large");
+  if (M == 0) return MQ_OK;
+  int64_t kc = 0;
+  if (G > 0) {
+    MQ_CHECK_ARG(group_size >= 32 && group_size % 32 == 0 && (128 % group_size == 0 || group_size % 128 == 0),
+                 "mq_mixed_gemm: group_size=%d must be 32, 64 or a multiple of 128", group_size);
+    kc = (G * group_size + 127) / 128 * 128;
+    MQ_CHECK_ARG(a_codes && w_codes && a_scales && w_scales, "mq_mixed_gemm: null code / scale pointer");
+    MQ_CHECK_ARG(lda >= kc && ldw >= kc && lda % 16 == 0 && ldw % 16 == 0,
+                 "mq_mixed_gemm: lda=%lld ldw=%lld must be multiples of 16 and >= %lld", (long long)lda,
+                 (long long)ldw, (long long)kc);
+    MQ_CHECK_ARG(reinterpret_cast<uintptr_t>(a_codes) % 16 == 0 && reinterpret_cast<uintptr_t>(w_codes) % 16 == 0,
+                 "mq_mixed_gemm: code pointers must be 16-byte aligned");
+    MQ_CHECK_ARG(ld_as >= M && ld_ws >= N && ld_ws % 4 == 0 && reinterpret_cast<uintptr_t>(w_scales) % 16 == 0,
+                 "mq_mixed_gemm: scales need ld_as >= M, ld_ws >= N, ld_ws %% 4 == 0, 16-byte aligned w_scales");
+  }
+  if (Ks > 0) {
+    MQ_CHECK_ARG(a_sal && w_sal && ld_asal >= Ks && ld_wsal >= Ks && ld_asal % 8 == 0 && ld_wsal % 8 == 0,
+                 "mq_mixed_gemm: salient operands need ld >= Ks and ld %% 8 == 0");
+    MQ_CHECK_ARG(reinterpret_cast<uintptr_t>(a_sal) % 16 == 0 && reinterpret_cast<uintptr_t>(w_sal) % 16 == 0,
+                 "mq_mixed_gemm: salient pointers must be 16-byte aligned");
+  }
+  int bn = mq_get_option("gemm_bn", 0);
+  if (bn != 128 && bn != 256) bn = N >= 256 ? 256 : 128;
+
+  CUtensorMap ma, mw, mas, mws;
+  int rc;
+  if (G > 0) {
+    if ((rc = make_map(&ma, a_codes, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, M, kc, lda, BM))) return rc;
+    if ((rc = make_map(&mw, w_codes, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, N, kc, ldw, bn))) return rc;
+  }
+  const CUtensorMapDataType dt16 = dtype == MQ_F16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+  if (Ks > 0) {  // the tensor maps cover exactly Ks columns: TMA zero-fills the tail of the last 64-column block
+    if ((rc = make_map(&mas, a_sal, dt16, 2, M, Ks, ld_asal, BM))) return rc;
+    if ((rc = make_map(&mws, w_sal, dt16, 2, N, Ks, ld_wsal, bn))) return rc;
+  } else {
+    mas = ma;
+    mws = mw;
+  }
+  if (G == 0) {
+    ma = mas;
+    mw = mws;
+  }
+  GemmArgs p{};
+  p.a_scales = a_scales; p.ld_as = ld_as; p.w_scales = w_scales; p.ld_ws = ld_ws; p.bias = bias;
+  p.y = y; p.ldy = ldy; p.M = (int)M; p.N = (int)N; p.G = (int)G; p.g = G > 0 ? group_size : 32;
+  p.kb_int = (int)(kc / 128); p.kb_sal = (int)((Ks + 63) / 64);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (dtype == MQ_F16) return dispatch_gemm<__half>(ma, mw, mas, mws, p, bn, st);
+  return dispatch_gemm<__nv_bfloat16>(ma, mw, mas, mws, p, bn, st);
+}
+
+// debug: fault record of the GEMM's bounded waits (see ptx.cuh); clears it.  Synchronises the device.
+int mq_gemm_fault(unsigned int* out8_host) {
+  unsigned int z[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  MQ_CHECK_CUDA(cudaMemcpyFromSymbol(out8_host, g_mq_fault, sizeof(z)));
+  MQ_CHECK_CUDA(cudaMemcpyToSymbol(g_mq_fault, z, sizeof(z)));
+  return MQ_OK;
+}
+
+}  // extern "C"

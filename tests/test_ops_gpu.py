@@ -1,0 +1,274 @@
+"""GPU parity tests of the C-ABI kernels (through smoothquant_mixedprecision_b200.ops -> ctypes -> libmq.so) against
+the CPU oracle and the reference-generated golden fixtures.  Integer / code / scale / permutation results are
+compared bit for bit; the GEMM within a stated tolerance."""
+import pytest
+import torch
+
+from oracle import mq_oracle as O
+
+pytestmark = pytest.mark.gpu
+
+DEV = "cuda"
+
+
+@pytest.fixture(scope="module")
+def ops():
+    from smoothquant_mixedprecision_b200 import ops as _ops
+    return _ops
+
+
+@pytest.fixture(scope="module")
+def mqlib():
+    from smoothquant_mixedprecision_b200 import _lib
+    return _lib
+
+
+def synth(rows, cols, dtype, seed, outliers=True):
+    g = torch.Generator().manual_seed(seed)
+    x = torch.randn(rows, cols, generator=g)
+    scale = torch.exp(0.5 * torch.randn(cols, generator=g))
+    if outliers:
+        idx = torch.randperm(cols, generator=g)[: max(1, cols // 100)]
+        scale[idx] *= torch.empty(idx.numel()).uniform_(10, 40, generator=g)
+    return (x * scale).to(dtype)
+
+
+# ------------------------------------------------------------------------------------------------ K0 / K0b
+@pytest.mark.parametrize("shape,dtype", [((64, 256), torch.float16), ((33, 777), torch.float16),
+                                         ((1000, 4096), torch.bfloat16), ((17, 130), torch.float32),
+                                         ((4096, 1024), torch.float16)])
+def test_colstat(ops, shape, dtype):
+    x = synth(*shape, dtype, seed=shape[0])
+    xg = x.to(DEV)
+    assert torch.equal(ops.colstat(xg, "max").cpu(), O.sort_key(x, "max").float())          # fake_quant.py:113
+    mean = x.abs().double().mean(dim=0).float()
+    assert torch.allclose(ops.colstat(xg, "mean").cpu(), mean, rtol=1e-6, atol=0)            # run_experiments.py:60
+    assert torch.allclose(ops.colstat(xg, "mean3std").cpu(), O.sort_key(x, "mean3std"), rtol=2e-4, atol=1e-6)
+    assert torch.equal(ops.colstat(xg, "argmax").cpu(), O.sort_key(x, "argmax"))
+
+
+@pytest.mark.parametrize("n", [1, 5, 255, 256, 4096, 11008])
+def test_argsort_stable(ops, n):
+    g = torch.Generator().manual_seed(n)
+    key = torch.randint(0, max(2, n // 3), (n,), generator=g).float()       # many ties
+    kg = key.to(DEV)
+    assert torch.equal(ops.argsort_stable(kg).cpu().long(), O.stable_argsort(key))
+    assert torch.equal(ops.argsort_stable(kg, descending=True).cpu().long(), O.stable_argsort(key, descending=True))
+    if n >= 5:
+        subset = torch.sort(torch.randperm(n, generator=g)[: n - n // 4]).values
+        want = subset[O.stable_argsort(key[subset])]
+        got = ops.argsort_stable(kg, subset=subset.to(DEV).int()).cpu().long()
+        assert torch.equal(got, want)
+
+
+# ------------------------------------------------------------------------------------------------ K1 / P0
+def _check_quant_rows(ops, x, g, n_bits, perm, sal, smooth=None):
+    xs = x if smooth is None else (x / smooth)
+    want = O.group_quant(xs[:, perm], n_bits, g)
+    q = ops.quant_rows(x.to(DEV), perm.to(DEV), sal.to(DEV) if sal is not None else None, g, n_bits,
+                       smooth=None if smooth is None else smooth.to(DEV))
+    G = want.scales.shape[1]
+    codes = q.codes.cpu()
+    assert torch.equal(codes[:, : G * g], want.codes)
+    assert int(codes[:, G * g:].abs().max()) == 0 if codes.shape[1] > G * g else True
+    assert torch.equal(q.scales.cpu()[:, : x.shape[0]].t(), want.scales.float())
+    if sal is not None:
+        s = q.sal.cpu()
+        assert torch.equal(s[:, : sal.numel()], xs[:, sal])
+        assert float(s[:, sal.numel():].abs().sum()) == 0.0
+
+
+def test_quant_rows_matches_oracle_on_golden_inputs(ops, golden_quantisers, mqlib):
+    for force in (0, 1):
+        mqlib.set_option("quant_force_generic", force)
+        try:
+            for i, c in enumerate(golden_quantisers):
+                x = c["x"].reshape(-1, c["x"].shape[-1])
+                K = x.shape[1]
+                gen = torch.Generator().manual_seed(100 + i)
+                order = torch.randperm(K, generator=gen)
+                ks = max(1, K // 20)
+                sal = torch.sort(order[:ks]).values
+                perm = order[ks:]
+                _check_quant_rows(ops, x, c["group_size"], c["n_bits"], perm, sal)
+        finally:
+            mqlib.set_option("quant_force_generic", 0)
+
+
+@pytest.mark.parametrize("R,K,g,dtype", [(64, 1024, 64, torch.float16), (37, 4096, 128, torch.float16),
+                                         (16, 2048, 1024, torch.float16), (50, 512, 32, torch.bfloat16),
+                                         (9, 768, 128, torch.float32), (130, 11008, 128, torch.float16),
+                                         (3, 256, 16, torch.float16)])
+def test_quant_rows_fast_path(ops, R, K, g, dtype):
+    x = synth(R, K, dtype, seed=R + K)
+    gen = torch.Generator().manual_seed(R)
+    order = torch.randperm(K, generator=gen)
+    ks = max(1, int(0.05 * K))
+    _check_quant_rows(ops, x, g, 4, order[ks:], torch.sort(order[:ks]).values)
+    _check_quant_rows(ops, x, g, 4, torch.arange(K), None)                     # no salient, identity order
+    if dtype != torch.float32:
+        sm = (torch.rand(K, generator=gen) + 0.5).to(dtype)
+        _check_quant_rows(ops, x, g, 4, order[ks:], torch.sort(order[:ks]).values, smooth=sm)
+
+
+def test_quant_rows_zero_rows_and_nbits8(ops):
+    x = torch.zeros(8, 256, dtype=torch.float16)
+    _check_quant_rows(ops, x, 128, 4, torch.arange(256), None)                 # all-zero groups: scale = fp16(1e-5)/7
+    x = synth(8, 256, torch.float16, 3)
+    _check_quant_rows(ops, x, 64, 8, torch.arange(256), None)
+
+
+def test_fakequant_rows_matches_reference_outputs(ops, golden_quantisers):
+    for c in golden_quantisers:
+        x = c["x"]
+        xg = x.to(DEV)
+        perm = c["act_group_sort_perm"]
+        out = ops.fakequant_rows(xg, perm.to(DEV), c["group_size"], c["n_bits"])
+        assert torch.equal(out.cpu(), c["act_group_sort"])                       # fake_quant.py:105-154
+        assert torch.equal(xg.cpu(), x)                                          # input untouched
+        out2 = ops.fakequant_rows(xg, None, c["group_size"], c["n_bits"])
+        assert torch.equal(out2.cpu(), c["act_group"])                           # fake_quant.py:78-101
+        if "weight_group_sort" in c:
+            outw = ops.fakequant_rows(xg, c["weight_group_sort_perm"].to(DEV), c["group_size"], c["n_bits"])
+            assert torch.equal(outw.cpu(), c["weight_group_sort"])               # fake_quant.py:157-207
+        if "act_token" in c:
+            x2 = x.reshape(-1, x.shape[-1])
+            tok = ops.fakequant_rows(xg, None, x2.shape[1], 4)
+            assert torch.equal(tok.cpu(), c["act_token"])                        # fake_quant.py:57-64
+            ten = ops.fakequant_tensor(xg, 4)
+            assert torch.equal(ten.cpu(), c["act_tensor"])                       # fake_quant.py:68-75
+            z = xg.clone()
+            r = ops.fakequant_rows(z, None, x2.shape[1], 4, inplace=True)
+            assert r.data_ptr() == z.data_ptr() and torch.equal(z.cpu(), c["act_token"])
+
+
+def test_dynamic_sort_pipeline_equals_reference_on_tie_free_keys(ops, golden_quantisers):
+    n = 0
+    for c in golden_quantisers:
+        x = c["x"].reshape(-1, c["x"].shape[-1])
+        key = O.sort_key(x, "max")
+        if key.unique().numel() != key.numel():
+            continue
+        n += 1
+        xg = c["x"].to(DEV)
+        perm = ops.argsort_stable(ops.colstat(xg, "max"))
+        assert torch.equal(perm.cpu().long(), c["act_group_sort_perm"])
+        out = ops.fakequant_rows(xg, perm, c["group_size"], c["n_bits"])
+        assert torch.equal(out.cpu(), c["act_group_sort"])
+    assert n >= 1
+
+
+def test_fakequant_passthrough_of_unlisted_columns(ops):
+    x = synth(20, 512, torch.float16, 5)
+    sal = torch.tensor([3, 77, 300, 511])
+    keep = O.nonsalient_columns(512, sal)
+    want = x.clone()
+    want[:, keep] = O.group_quant(x[:, keep], 4, 128).deq
+    got = ops.fakequant_rows(x.to(DEV), keep.to(DEV), 128, 4)
+    assert torch.equal(got.cpu(), want)
+
+
+def test_fast_and_generic_kernels_agree_at_full_size(ops, mqlib):
+    x = synth(2048, 4096, torch.float16, 11).to(DEV)
+    order = torch.randperm(4096, generator=torch.Generator().manual_seed(1))
+    perm, sal = order[204:].to(DEV), torch.sort(order[:204]).values.to(DEV)
+    a = ops.quant_rows(x, perm, sal, 128)
+    d = ops.fakequant_rows(x, perm, 128)
+    mqlib.set_option("quant_force_generic", 1)
+    try:
+        b = ops.quant_rows(x, perm, sal, 128)
+        e = ops.fakequant_rows(x, perm, 128)
+    finally:
+        mqlib.set_option("quant_force_generic", 0)
+    assert torch.equal(a.codes, b.codes) and torch.equal(a.scales, b.scales) and torch.equal(a.sal, b.sal)
+    assert torch.equal(d, e)
+    # properties: |codes| <= 7, each group attains 7 somewhere unless it is all zero, dequantisation is idempotent
+    assert int(a.codes.abs().max()) == 7
+    assert torch.equal(ops.fakequant_rows(d, perm, 128), d)
+    assert mqlib.quant_fault()[0] == 0
+
+
+def test_int4_pack_roundtrip(ops):
+    codes = torch.randint(-7, 8, (33, 256), dtype=torch.int8)
+    packed = ops.pack_int4(codes.to(DEV))
+    assert torch.equal(packed.cpu(), O.int4_pack(codes))
+    assert torch.equal(ops.unpack_int4(packed).cpu(), codes)
+
+
+# ------------------------------------------------------------------------------------------------ K2
+def _gemm_reference(a, w, bias, Ks, M, N):
+    """fp32 composition on the GPU from integer codes and scales (exact partial sums: |sum| < 2^24)."""
+    ref = torch.zeros(M, N, dtype=torch.float32, device=DEV)
+    g = a.group_size
+    for gi in range(a.groups):
+        p = a.codes[:, gi * g:(gi + 1) * g].float() @ w.codes[:, gi * g:(gi + 1) * g].float().t()
+        ref += p * (a.scales[gi, :M, None] * w.scales[gi, None, :N])
+    if Ks:
+        ref += a.sal[:, :Ks].float() @ w.sal[:, :Ks].float().t()
+    if bias is not None:
+        ref += bias.float()
+    return ref
+
+
+@pytest.mark.parametrize("M,N,K,g,p,dtype,bn", [
+    (128, 128, 512, 128, 0.05, torch.float16, 128),
+    (24, 192, 256, 64, 0.05, torch.float16, 128),
+    (300, 328, 1024, 64, 0.10, torch.float16, 128),
+    (512, 768, 2048, 128, 0.05, torch.bfloat16, 256),
+    (1000, 1024, 4096, 128, 0.05, torch.float16, 256),
+    (256, 512, 4096, 1024, 0.0, torch.float16, 256),
+    (2048, 4096, 4096, 128, 0.05, torch.float16, 256),
+])
+def test_mixed_gemm_matches_composed_reference(ops, mqlib, M, N, K, g, p, dtype, bn):
+    x = synth(M, K, dtype, seed=M + N).to(DEV)
+    w = (torch.randn(N, K, generator=torch.Generator().manual_seed(N)) * 0.02).to(dtype).to(DEV)
+    bias = (torch.randn(N, generator=torch.Generator().manual_seed(7)) * 0.1).to(dtype).to(DEV)
+    order = torch.randperm(K, generator=torch.Generator().manual_seed(K))
+    ks = max(1, int(p * K)) if p > 0 else 0
+    perm = order[ks:].to(DEV)
+    sal = torch.sort(order[:ks]).values.to(DEV) if ks else None
+    a = ops.quant_rows(x, perm, sal, g)
+    wq = ops.quant_rows(w, perm, sal, g)
+    mqlib.set_option("gemm_bn", bn)
+    try:
+        y = ops.mixed_gemm(a, wq, bias)
+        torch.cuda.synchronize()
+    finally:
+        mqlib.set_option("gemm_bn", 0)
+    assert mqlib.gemm_fault()[0] == 0
+    ref = _gemm_reference(a, wq, bias, ks, M, N)
+    # tolerance: output rounding to fp16 (2^-11) / bf16 (2^-8) relative + fp32 accumulation-order noise
+    rtol = 1e-3 if dtype == torch.float16 else 8e-3
+    err = (y.float() - ref).abs()
+    assert float((err - rtol * ref.abs()).max()) <= 2e-3 * float(ref.abs().max())
+    assert float(err.norm() / ref.norm()) < (5e-4 if dtype == torch.float16 else 4e-3)
+
+
+def test_mixed_gemm_against_cpu_oracle_on_golden_layer(ops, golden_layers):
+    """Full fused path (K1 on both operands + K2) against oracle.fused_layer_oracle evaluated in float64."""
+    c = golden_layers[0]
+    K, g = c["K"], c["group_size"]
+    x = c["x"].reshape(-1, K)
+    part = O.fused_partition(K, c["salient_indices"], O.sort_key(x, "max").float(), g)
+    y64, aq, wq = O.fused_layer_oracle(x, c["weight_fp"], c["bias"], part)
+    perm, sal = part.perm.to(DEV), part.salient.to(DEV)
+    a = ops.quant_rows(x.to(DEV), perm, sal, g)
+    w = ops.quant_rows(c["weight_fp"].to(DEV), perm, sal, g)
+    G = aq.scales.shape[1]
+    assert torch.equal(a.codes.cpu()[:, : G * g], aq.codes) and torch.equal(w.codes.cpu()[:, : G * g], wq.codes)
+    assert torch.equal(a.scales.cpu()[:, : x.shape[0]].t(), aq.scales.float())
+    assert torch.equal(w.scales.cpu()[:, : c["N"]].t(), wq.scales.float())
+    bias = c["bias"].reshape(-1).to(DEV) if c["bias"] is not None else None
+    y = ops.mixed_gemm(a, w, bias).cpu().double()
+    err = (y - y64).abs()
+    assert float(err.max()) <= 1e-3 * float(y64.abs().max()) + 1e-3       # fp16 output rounding of |y| <~ 10
+
+
+def test_pure_f16_gemm_reference_mode(ops):
+    M, N, K = 200, 328, 520                                                   # K not a multiple of 64: TMA zero fill
+    a = torch.randn(M, K, generator=torch.Generator().manual_seed(1)).half().to(DEV)
+    w = (torch.randn(N, K, generator=torch.Generator().manual_seed(2)) * 0.05).half().to(DEV)
+    b = torch.randn(N, generator=torch.Generator().manual_seed(3)).half().to(DEV)
+    y = ops.mixed_gemm(None, None, b, a_sal=a, w_sal=w)
+    ref = a.float() @ w.float().t() + b.float()
+    assert float((y.float() - ref).abs().max()) <= 2e-3 * float(ref.abs().max())
