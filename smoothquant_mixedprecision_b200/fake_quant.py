@@ -1,0 +1,433 @@
+"""Module-swap API of the W4A4 MixedQuant linear path, B200-native.
+
+Mirrors the public surface of the reference's ``smoothquant/fake_quant.py`` (names, argument order, defaults and
+exception types) so that ``from smoothquant.fake_quant import W4A4Linear, quantize_model, ...`` keeps working, but
+every tensor operation on the path is a hand-written sm_100a kernel reached through the C ABI of ``include/mq.h``
+(``ops`` -> ctypes -> ``libmq.so``).  There is no CPU fallback: tensors must live on a CUDA device.
+
+Two execution modes (SURVEY.md 8(a')):
+
+``mode="reference"``  literal semantics of the reference layer.  Activations: the non-salient columns are compacted,
+    sorted by their per-call column abs-max and grouped (fake_quant.py:291-301 -> :105-154); weights: ALL K columns
+    are sorted by the weight's own column abs-max, grouped, and the salient columns restored afterwards
+    (fake_quant.py:347-365).  The two operands use different K partitions, so the contraction runs on dequantised
+    16-bit values (tcgen05 kind::f16).  Kernels: K0 column stats -> K0b stable argsort -> K1 fake-quantise -> K2.
+
+``mode="fused"``  the fast path named by BASELINE.json: ONE static permutation of the non-salient columns shared by
+    both operands, activations quantised to integer codes + per-(token, group) scales by K1, weights packed offline
+    by the same kernel, contraction as tcgen05 kind::i8 per K group with an fp32 rescale plus the salient slice as
+    kind::f16 in the same CTA (K2).  Codes / scales are bit-exact against the reference's natural-order group
+    quantisers (fake_quant.py:78-101, :30-53) applied to ``x[:, perm]`` / ``W[:, perm]``.
+
+``torch.argsort`` in the reference is unstable under ties; this implementation always orders ties by
+ascending index and accepts an explicit permutation where parity against a recorded reference run is wanted.
+"""
+from __future__ import annotations
+
+from typing import Dict, Optional
+
+import torch
+from torch import nn
+
+from . import ops
+
+__all__ = [
+    "quantize_weight_per_channel_absmax", "quantize_weight_per_tensor_absmax", "quantize_weight_per_group_absmax",
+    "quantize_activation_per_token_absmax", "quantize_activation_per_tensor_absmax",
+    "quantize_activation_per_group_absmax", "quantize_activation_per_group_absmax_sort",
+    "quantize_weight_per_group_absmax_sort", "W4A4Linear", "quantize_opt", "quantize_llama_like", "quantize_model",
+]
+
+SORT_KINDS = ("max", "mean3std", "argmax", "none")
+MODES = ("reference", "fused")
+_ACT_QUANTS = ("per_token", "per_tensor", "per_group")
+_WEIGHT_QUANTS = ("per_channel", "per_tensor", "per_group")
+
+
+# ------------------------------------------------------------------------------------------- quantiser functions
+# Same names / positional arguments as the reference.  Each returns the fake-quantised (dequantised) tensor in the
+# input dtype.  Like the reference, the per-token / per-tensor / per-channel variants overwrite their argument
+# (in-place div_/round_/mul_, fake_quant.py:15, :25, :63, :74); the per-group variants never touch it.
+
+@torch.no_grad()
+def quantize_weight_per_channel_absmax(w, n_bits=4):
+    """fake_quant.py:10-16 -- one scale per output channel (row); in place."""
+    return ops.fakequant_rows(w, None, w.shape[-1], n_bits, inplace=True)
+
+
+@torch.no_grad()
+def quantize_weight_per_tensor_absmax(w, n_bits=4):
+    """fake_quant.py:20-26 -- one global scale; in place."""
+    return ops.fakequant_tensor(w, n_bits, inplace=True)
+
+
+@torch.no_grad()
+def quantize_weight_per_group_absmax(w, n_bits=4, group_size=128):
+    """fake_quant.py:30-53 -- natural-order groups of ``group_size`` input columns per output row."""
+    return ops.fakequant_rows(w, None, group_size, n_bits)
+
+
+@torch.no_grad()
+def quantize_activation_per_token_absmax(t, n_bits=4):
+    """fake_quant.py:57-64 -- one scale per token (row of the flattened tensor); in place."""
+    return ops.fakequant_rows(t, None, t.shape[-1], n_bits, inplace=True)
+
+
+@torch.no_grad()
+def quantize_activation_per_tensor_absmax(t, n_bits=4):
+    """fake_quant.py:68-75 -- one global scale; in place."""
+    return ops.fakequant_tensor(t, n_bits, inplace=True)
+
+
+@torch.no_grad()
+def quantize_activation_per_group_absmax(t, n_bits=4, group_size=128):
+    """fake_quant.py:78-101 -- natural-order groups along the last dimension."""
+    return ops.fakequant_rows(t, None, group_size, n_bits)
+
+
+def _dynamic_perm(t2d: torch.Tensor, subset: Optional[torch.Tensor] = None, kind: str = "max") -> torch.Tensor:
+    """Ascending stable argsort of the column statistic over ALL rows (fake_quant.py:113-116, :164-167)."""
+    if kind == "none":
+        return subset if subset is not None else torch.arange(t2d.shape[-1], dtype=torch.int32, device=t2d.device)
+    return ops.argsort_stable(ops.colstat(t2d, kind), subset=subset)
+
+
+@torch.no_grad()
+def quantize_activation_per_group_absmax_sort(t, n_bits=4, group_size=128, perm=None):
+    """fake_quant.py:105-154 -- sort channels by max |t| over every row, group, quantise, undo the permutation.
+    ``perm`` (optional, extension) replays a recorded permutation instead of computing one."""
+    if perm is None:
+        perm = _dynamic_perm(t.reshape(-1, t.shape[-1]))
+    return ops.fakequant_rows(t, perm, group_size, n_bits)
+
+
+@torch.no_grad()
+def quantize_weight_per_group_absmax_sort(w, n_bits=4, group_size=128, perm=None):
+    """fake_quant.py:157-207 -- the same algorithm on w [N, K]; the key is the per-input-column max over rows."""
+    if perm is None:
+        perm = _dynamic_perm(w)
+    return ops.fakequant_rows(w, perm, group_size, n_bits)
+
+
+# ------------------------------------------------------------------------------------------- the layer
+def _check_choice(value, allowed, what):
+    if value not in allowed:
+        raise ValueError(f"Invalid {what}: {value}")
+
+
+class W4A4Linear(nn.Module):
+    """Drop-in for the reference's ``W4A4Linear`` (fake_quant.py:209-374).
+
+    Constructor arguments, attribute names (``in_features out_features group_size weight bias salient_indices
+    act_quant_name weight_quant_name output_quant_name``), ``from_float`` and ``__repr__`` follow the reference;
+    ``mode`` / ``sort`` / ``sort_key`` are new, defaulted keyword arguments.
+    """
+
+    def __init__(self, in_features, out_features, bias=True, act_quant="per_token", quantize_output=False,
+                 importance=None, salient_prop=0, quant_bits=4, group_size=128, mode="reference", sort="max",
+                 device=None, dtype=torch.float16):
+        super().__init__()
+        _check_choice(act_quant, _ACT_QUANTS, "act_quant")          # ValueError like fake_quant.py:256
+        _check_choice(mode, MODES, "mode")
+        _check_choice(sort, SORT_KINDS, "sort")
+        self.in_features = in_features
+        self.out_features = out_features
+        self.group_size = group_size
+        self.quant_bits = quant_bits
+        self.mode = mode
+        self.sort = sort
+        self.act_quant_name = act_quant
+        self.output_quant_name = act_quant if quantize_output else "None"
+        self.weight_quant_name = "None"
+        # the reference allocates (and later discards) an fp16 randn weight here (fake_quant.py:227-235); an empty
+        # placeholder of the same shape / dtype keeps `.weight.shape` meaningful without the wasted RNG pass
+        self.register_buffer("_weight", torch.empty((out_features, in_features), dtype=dtype, device=device))
+        self.register_buffer("bias", torch.zeros((1, out_features), dtype=dtype, device=device) if bias else None)
+        # fused-mode operands (filled by from_float)
+        for name in ("w_codes", "w_scales", "w_sal", "perm", "sal_sorted", "keep"):
+            self.register_buffer(name, None)
+        self.salient_indices = None
+        if importance is not None and salient_prop > 0:
+            # fake_quant.py:265-270 -- top max(1, int(p*K)) channels by importance, canonical tie order
+            imp = torch.as_tensor(importance).float()
+            order = torch.argsort(imp, descending=True, stable=True)
+            self.salient_indices = order[: max(1, int(salient_prop * len(order)))]
+
+    # ---- reference-compatible `weight` attribute: a stored buffer in reference mode, a lazily dequantised view of
+    # the packed operands in fused mode
+    @property
+    def weight(self):
+        if self.mode == "fused" and self.w_codes is not None:
+            return self.dequantized_weight()
+        return self._weight
+
+    @weight.setter
+    def weight(self, value):
+        self._buffers["_weight"] = value
+
+    def to(self, *args, **kwargs):
+        # fake_quant.py:272-277 moves weight and bias explicitly; buffers registered here move with nn.Module.to
+        super().to(*args, **kwargs)
+        return self
+
+    def _device_indices(self, device):
+        """int32 device copies of the salient list (sorted ascending) and of its complement, cached per device (the
+        reference re-uploads a CPU LongTensor on every forward)."""
+        if self.salient_indices is None:
+            return None, None
+        if self.sal_sorted is None or self.sal_sorted.device != device:
+            sal = torch.sort(self.salient_indices.to(torch.int64)).values
+            mask = torch.ones(self.in_features, dtype=torch.bool)
+            mask[sal.cpu()] = False
+            self.sal_sorted = sal.to(device=device, dtype=torch.int32)
+            self.keep = torch.nonzero(mask).flatten().to(device=device, dtype=torch.int32)
+        return self.sal_sorted, self.keep
+
+    # ---- activation / output fake quantiser of mode="reference" (fake_quant.py:291-304, :309-316)
+    def _fake_quant_nonsalient(self, t2d, name, perm=None):
+        _, keep = self._device_indices(t2d.device)
+        if keep is not None and keep.numel() == 0:
+            return t2d.clone()
+        if name == "per_group":
+            if perm is None:
+                perm = keep if self.sort == "none" else _dynamic_perm(t2d, subset=keep, kind=self.sort)
+            return ops.fakequant_rows(t2d, perm, self.group_size, self.quant_bits)
+        if name == "per_token":
+            if keep is None:    # the reference quantises x itself in place (fake_quant.py:63)
+                return ops.fakequant_rows(t2d, None, t2d.shape[-1], self.quant_bits, inplace=True)
+            return ops.fakequant_rows(t2d, keep, keep.numel(), self.quant_bits)
+        if name == "per_tensor":
+            if keep is None:
+                return ops.fakequant_tensor(t2d, self.quant_bits, inplace=True)
+            out = t2d.clone()
+            k64 = keep.long()
+            out[:, k64] = ops.fakequant_tensor(t2d[:, k64].contiguous(), self.quant_bits, inplace=True)
+            return out
+        raise ValueError(f"Invalid act_quant: {name}")
+
+    @torch.no_grad()
+    def forward(self, x, act_perm=None, out_perm=None):
+        shape = x.shape
+        if x.dim() == 3:
+            x2 = x.reshape(-1, shape[-1])
+        elif x.dim() == 2:
+            x2 = x
+        else:
+            raise ValueError(f"Unsupported input shape: {shape}")       # fake_quant.py:287
+        if self.mode == "fused":
+            y = self._forward_fused(x2)
+        else:
+            y = self._forward_reference(x2, act_perm, out_perm)
+        return y.view(shape[0], shape[1], -1) if x.dim() == 3 else y
+
+    def _forward_fused(self, x2):
+        cdt = self.w_sal.dtype if self.w_sal is not None else (
+            x2.dtype if x2.dtype in (torch.float16, torch.bfloat16) else torch.float16)
+        xin = x2 if x2.dtype == cdt else x2.to(cdt)
+        a = ops.quant_rows(xin, self.perm, self.sal_sorted, self.group_size, self.quant_bits,
+                           Kn=0 if self.perm is None else self.perm.numel())
+        w = ops.QuantizedRows(codes=self.w_codes, scales=self.w_scales, sal=self.w_sal, rows=self.out_features,
+                              Kn=a.Kn, Ks=a.Ks, group_size=self.group_size)
+        y = ops.mixed_gemm(a, w, self.bias, out_dtype=cdt)
+        if self.output_quant_name != "None":
+            y = self._quantize_output(y)
+        return y if y.dtype == x2.dtype else y.to(x2.dtype)
+
+    def _forward_reference(self, x2, act_perm, out_perm):
+        q_x = self._fake_quant_nonsalient(x2, self.act_quant_name, act_perm)
+        w = self._weight
+        cdt = w.dtype if w.dtype in (torch.float16, torch.bfloat16) else torch.float16
+        # F.linear(q_x, weight, bias) (fake_quant.py:306) as the pure 16-bit tcgen05 GEMM; fp32 modules (OPT, SURVEY
+        # F7) are cast to fp16 at the boundary -- stated tolerance in tests/DESIGN.md
+        y = ops.mixed_gemm(None, None, self.bias, a_sal=q_x if q_x.dtype == cdt else q_x.to(cdt),
+                           w_sal=w if w.dtype == cdt else self._weight16(cdt))
+        if y.dtype != x2.dtype:
+            y = y.to(x2.dtype)
+        if self.output_quant_name != "None":
+            y = self._quantize_output(y, out_perm)
+        return y
+
+    def _weight16(self, cdt):
+        cache = getattr(self, "_w16_cache", None)
+        if cache is None or cache.dtype != cdt or cache.device != self._weight.device:
+            cache = self._weight.to(cdt)
+            object.__setattr__(self, "_w16_cache", cache)
+        return cache
+
+    def _quantize_output(self, y, out_perm=None):
+        # fake_quant.py:309-316: the K-sized input mask indexes y's columns -> only valid when N == K
+        if self.salient_indices is not None and self.out_features != self.in_features:
+            raise IndexError(f"The shape of the mask [{self.in_features}] at index 0 does not match the shape of the "
+                             f"indexed tensor [{y.shape[0]}, {self.out_features}] at index 1")
+        return self._fake_quant_nonsalient(y.contiguous(), self.output_quant_name, out_perm)
+
+    # ---- offline weight path
+    @staticmethod
+    @torch.no_grad()
+    def from_float(module, weight_quant="per_channel", act_quant="per_token", quantize_output=False, importance=None,
+                   salient_prop=0, quant_bits=4, group_size=128, mode="reference", sort="max", sort_key=None,
+                   weight_perm=None):
+        assert isinstance(module, torch.nn.Linear)                                    # fake_quant.py:335
+        _check_choice(weight_quant, _WEIGHT_QUANTS, "weight_quant")                   # ValueError, fake_quant.py:361
+        w = module.weight.data
+        if not w.is_cuda:
+            raise RuntimeError("W4A4Linear.from_float needs the module on a CUDA device (no CPU fallback)")
+        new = W4A4Linear(module.in_features, module.out_features, module.bias is not None, act_quant=act_quant,
+                         quantize_output=quantize_output, importance=importance, salient_prop=salient_prop,
+                         quant_bits=quant_bits, group_size=group_size, mode=mode, sort=sort, device="meta",
+                         dtype=w.dtype)
+        new._buffers["_weight"] = None
+        new.weight_quant_name = weight_quant
+        sal, keep = new._device_indices(w.device)
+        if mode == "fused":
+            if weight_quant != "per_group" or act_quant != "per_group":
+                raise ValueError("mode='fused' needs weight_quant='per_group' and act_quant='per_group'")
+            new._pack_fused(w, sort_key if sort_key is not None else importance)
+        else:
+            if weight_quant == "per_group":       # sorts ALL K columns by the weight's own abs-max (:164-167)
+                wq = quantize_weight_per_group_absmax_sort(w, quant_bits, group_size, perm=weight_perm)
+            elif weight_quant == "per_channel":   # the reference mutates module.weight here; so do we
+                wq = quantize_weight_per_channel_absmax(w if sal is None else w.clone(), quant_bits)
+            else:
+                wq = quantize_weight_per_tensor_absmax(w if sal is None else w.clone(), quant_bits)
+            if sal is not None:                   # FP originals back into the salient columns (:363-365)
+                s64 = sal.long()
+                wq[:, s64] = module.weight.data[:, s64]
+            new._buffers["_weight"] = wq
+        new._buffers["bias"] = None if module.bias is None else module.bias.data        # shape [N] (:369-370)
+        return new
+
+    def _pack_fused(self, w, key):
+        """P0 weight packer: static shared permutation (non-salient columns stably sorted by ``key`` ascending),
+        codes + group scales of W[:, perm] (== quantize_weight_per_group_absmax, fake_quant.py:30-53) and the
+        salient columns in the weight dtype."""
+        dev = w.device
+        sal, keep = self._device_indices(dev)
+        if keep is None:
+            keep = torch.arange(self.in_features, dtype=torch.int32, device=dev)
+        if self.sort == "none" or key is None:
+            perm = keep
+        else:
+            key = torch.as_tensor(key).to(device=dev, dtype=torch.float32)
+            perm = ops.argsort_stable(key, subset=keep)
+        cdt = w.dtype if w.dtype in (torch.float16, torch.bfloat16) else torch.float16
+        wq = ops.quant_rows(w if w.dtype == cdt else w.to(cdt), perm, sal, self.group_size, self.quant_bits)
+        self.perm = perm
+        self.w_codes, self.w_scales, self.w_sal = wq.codes, wq.scales, wq.sal
+
+    @torch.no_grad()
+    def dequantized_weight(self):
+        """[N, K] weight equivalent to the packed operands: code*scale at the original column of every permuted
+        position, the FP salient columns elsewhere (API compatibility; not on the hot path)."""
+        N, K, g = self.out_features, self.in_features, self.group_size
+        Kn = self.perm.numel()
+        G = (Kn + g - 1) // g
+        dt = self.w_sal.dtype if self.w_sal is not None else torch.float16
+        out = torch.zeros((N, K), dtype=dt, device=self.w_codes.device)
+        if Kn:
+            sc = self.w_scales[:G, :N].t().to(dt)                                      # exact: scales are dt values
+            deq = (self.w_codes[:, : G * g].view(N, G, g).to(dt) * sc[:, :, None]).view(N, G * g)[:, :Kn]
+            out[:, self.perm.long()] = deq
+        if self.sal_sorted is not None:
+            out[:, self.sal_sorted.long()] = self.w_sal[:, : self.sal_sorted.numel()]
+        return out
+
+    def packed_bytes(self) -> int:
+        """True storage of the layer (the reference's get_model_size stops counting quantised linears)."""
+        if self.mode == "fused" and self.w_codes is not None:
+            Kn = self.perm.numel()
+            n = self.out_features * ((Kn + 1) // 2) + self.w_scales.numel() * 2
+            if self.w_sal is not None:
+                n += self.out_features * self.sal_sorted.numel() * self.w_sal.element_size()
+            n += Kn * 4
+        else:
+            n = self._weight.numel() * self._weight.element_size()
+        if self.bias is not None:
+            n += self.bias.numel() * self.bias.element_size()
+        return n
+
+    def __repr__(self):
+        return (f"W4A4Linear({self.in_features}, {self.out_features}, bias={self.bias is not None}, "
+                f"weight_quant={self.weight_quant_name}, act_quant={self.act_quant_name}, "
+                f"output_quant={self.output_quant_name}, salient_indices={self.salient_indices})")
+
+
+# ------------------------------------------------------------------------------------------- model walkers
+def _importance(input_feat, key, guarded):
+    """sum over calibration blocks of mean|x| (fake_quant.py:396, :486).  The OPT walker has no guard and raises
+    KeyError / TypeError on a missing entry, the Llama walker maps an empty dict to None."""
+    if guarded and not input_feat:
+        return None
+    return sum(input_feat[key]).float()
+
+
+def _swap(parent, attr, prefix, input_feat, guarded, quantize_output, kw, extra):
+    imp = _importance(input_feat, prefix + "." + attr, guarded)
+    sk = extra.get("sort_keys")
+    setattr(parent, attr, W4A4Linear.from_float(
+        getattr(parent, attr), quantize_output=quantize_output, importance=imp,
+        sort_key=None if sk is None else sk.get(prefix + "." + attr),
+        mode=extra.get("mode", "reference"), sort=extra.get("sort", "max"), **kw))
+
+
+def quantize_opt(model, weight_quant="per_tensor", act_quant="per_tensor", quantize_bmm_input=True, input_feat=None,
+                 salient_prop=0, quant_bits=4, group_size=128, **extra):
+    """fake_quant.py:377-461 -- OPT: fc1, fc2 per decoder layer; q/k/v (output-quantised when quantize_bmm_input)
+    and out_proj per attention block."""
+    from transformers.models.opt.modeling_opt import OPTAttention, OPTDecoderLayer
+    kw = dict(weight_quant=weight_quant, act_quant=act_quant, salient_prop=salient_prop, quant_bits=quant_bits,
+              group_size=group_size)
+    for name, m in list(model.model.named_modules()):
+        prefix = "model." + name
+        if isinstance(m, OPTDecoderLayer):
+            for attr in ("fc1", "fc2"):
+                _swap(m, attr, prefix, input_feat, False, False, kw, extra)
+        elif isinstance(m, OPTAttention):
+            for attr in ("q_proj", "k_proj", "v_proj"):
+                _swap(m, attr, prefix, input_feat, False, quantize_bmm_input, kw, extra)
+            _swap(m, "out_proj", prefix, input_feat, False, False, kw, extra)
+    return model
+
+
+def quantize_llama_like(model, weight_quant="per_channel", act_quant="per_token", quantize_bmm_input=False,
+                        input_feat=None, salient_prop=0, quant_bits=4, group_size=128, **extra):
+    """fake_quant.py:464-561 -- Llama / Mistral: gate, up, down per MLP; q/k/v (+ optional output quant), o_proj."""
+    from transformers.models.llama.modeling_llama import LlamaAttention, LlamaMLP
+    from transformers.models.mistral.modeling_mistral import MistralAttention, MistralMLP
+    kw = dict(weight_quant=weight_quant, act_quant=act_quant, salient_prop=salient_prop, quant_bits=quant_bits,
+              group_size=group_size)
+    for name, m in list(model.model.named_modules()):
+        prefix = "model." + name
+        if isinstance(m, (LlamaMLP, MistralMLP)):
+            for attr in ("gate_proj", "up_proj", "down_proj"):
+                _swap(m, attr, prefix, input_feat, True, False, kw, extra)
+        elif isinstance(m, (LlamaAttention, MistralAttention)):
+            for attr in ("q_proj", "k_proj", "v_proj"):
+                _swap(m, attr, prefix, input_feat, True, quantize_bmm_input, kw, extra)
+            _swap(m, "o_proj", prefix, input_feat, True, False, kw, extra)
+    return model
+
+
+def quantize_model(model, weight_quant="per_channel", act_quant="per_token", quantize_bmm_input=False,
+                   input_feat=None, salient_prop=None, quant_bits=4, group_size=128, min_prop=0, max_prop=0, **extra):
+    """fake_quant.py:734-799 -- dispatch on the model family.  ``min_prop`` / ``max_prop`` are accepted and ignored
+    like in the reference.  Mixtral / Falcon walkers are out of scope: ValueError."""
+    if input_feat is None:
+        input_feat = {}
+    from transformers.models.llama.modeling_llama import LlamaPreTrainedModel
+    from transformers.models.mistral.modeling_mistral import MistralPreTrainedModel
+    from transformers.models.opt.modeling_opt import OPTPreTrainedModel
+    kw = dict(weight_quant=weight_quant, act_quant=act_quant, quantize_bmm_input=quantize_bmm_input,
+              input_feat=input_feat, salient_prop=salient_prop, quant_bits=quant_bits, group_size=group_size)
+    if isinstance(model, OPTPreTrainedModel):
+        return quantize_opt(model, **kw, **extra)
+    if isinstance(model, (LlamaPreTrainedModel, MistralPreTrainedModel)):
+        return quantize_llama_like(model, **kw, **extra)
+    raise ValueError(f"Unsupported model type: {type(model)}")
+
+
+def model_packed_bytes(model) -> Dict[str, int]:
+    """Real storage of the swapped linears vs everything else (replaces the analytic get_model_size)."""
+    lin = sum(m.packed_bytes() for m in model.modules() if isinstance(m, W4A4Linear))
+    other = sum(p.numel() * p.element_size() for p in model.parameters())
+    return {"w4a4_linear_bytes": lin, "other_parameter_bytes": other, "total_bytes": lin + other}
