@@ -50,37 +50,37 @@ _WEIGHT_QUANTS = ("per_channel", "per_tensor", "per_group")
 # (in-place div_/round_/mul_, fake_quant.py:15, :25, :63, :74); the per-group variants never touch it.
 
 @torch.no_grad()
-def quantize_weight_per_channel_absmax(w, n_bits=4):
+def quantize_weight_per_channel_absmax(w, n_bits):
     """fake_quant.py:10-16 -- one scale per output channel (row); in place."""
     return ops.fakequant_rows(w, None, w.shape[-1], n_bits, inplace=True)
 
 
 @torch.no_grad()
-def quantize_weight_per_tensor_absmax(w, n_bits=4):
+def quantize_weight_per_tensor_absmax(w, n_bits):
     """fake_quant.py:20-26 -- one global scale; in place."""
     return ops.fakequant_tensor(w, n_bits, inplace=True)
 
 
 @torch.no_grad()
-def quantize_weight_per_group_absmax(w, n_bits=4, group_size=128):
+def quantize_weight_per_group_absmax(w, n_bits, group_size=128):
     """fake_quant.py:30-53 -- natural-order groups of ``group_size`` input columns per output row."""
     return ops.fakequant_rows(w, None, group_size, n_bits)
 
 
 @torch.no_grad()
-def quantize_activation_per_token_absmax(t, n_bits=4):
+def quantize_activation_per_token_absmax(t, n_bits):
     """fake_quant.py:57-64 -- one scale per token (row of the flattened tensor); in place."""
     return ops.fakequant_rows(t, None, t.shape[-1], n_bits, inplace=True)
 
 
 @torch.no_grad()
-def quantize_activation_per_tensor_absmax(t, n_bits=4):
+def quantize_activation_per_tensor_absmax(t, n_bits):
     """fake_quant.py:68-75 -- one global scale; in place."""
     return ops.fakequant_tensor(t, n_bits, inplace=True)
 
 
 @torch.no_grad()
-def quantize_activation_per_group_absmax(t, n_bits=4, group_size=128):
+def quantize_activation_per_group_absmax(t, n_bits, group_size=128):
     """fake_quant.py:78-101 -- natural-order groups along the last dimension."""
     return ops.fakequant_rows(t, None, group_size, n_bits)
 
@@ -93,7 +93,7 @@ def _dynamic_perm(t2d: torch.Tensor, subset: Optional[torch.Tensor] = None, kind
 
 
 @torch.no_grad()
-def quantize_activation_per_group_absmax_sort(t, n_bits=4, group_size=128, perm=None):
+def quantize_activation_per_group_absmax_sort(t, n_bits, group_size=128, perm=None):
     """fake_quant.py:105-154 -- sort channels by max |t| over every row, group, quantise, undo the permutation.
     ``perm`` (optional, extension) replays a recorded permutation instead of computing one."""
     if perm is None:
@@ -102,7 +102,7 @@ def quantize_activation_per_group_absmax_sort(t, n_bits=4, group_size=128, perm=
 
 
 @torch.no_grad()
-def quantize_weight_per_group_absmax_sort(w, n_bits=4, group_size=128, perm=None):
+def quantize_weight_per_group_absmax_sort(w, n_bits, group_size=128, perm=None):
     """fake_quant.py:157-207 -- the same algorithm on w [N, K]; the key is the per-input-column max over rows."""
     if perm is None:
         perm = _dynamic_perm(w)

@@ -1,0 +1,78 @@
+"""CPU-side checks: the C-ABI library loads and exports every symbol include/mq.h declares, the Python surface keeps
+the reference's signatures, errors are raised before the ABI is crossed, and there is no CPU fallback."""
+import inspect
+import json
+import os
+import re
+
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_library_exports_every_declared_symbol():
+    from smoothquant_mixedprecision_b200 import _lib
+    hdr = open(os.path.join(ROOT, "include", "mq.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    declared = set(re.findall(r"\b(mq_[a-z0-9_]+)\s*\(", hdr))
+    assert declared, "no declarations parsed"
+    assert declared == set(_lib.SIGNATURES), declared ^ set(_lib.SIGNATURES)
+    for name in declared:
+        assert hasattr(_lib.lib, name), name
+    assert _lib.lib.mq_version() == 1
+    assert _lib.lib.mq_set_option(b"no_such_option", 1) == -1
+    assert b"unknown option" in _lib.lib.mq_last_error()
+
+
+def test_signatures_match_reference():
+    from smoothquant_mixedprecision_b200 import fake_quant as fq, smooth as sm
+    gold = json.load(open(os.path.join(ROOT, "tests", "golden", "signatures.json")))
+
+    def check(fn, want, skip_self=False):
+        got = [[p.name, None if p.default is inspect._empty else repr(p.default)]
+               for p in inspect.signature(fn).parameters.values() if p.kind != p.VAR_KEYWORD]
+        assert got[: len(want)] == want, (fn, got, want)
+        assert all(d is not None for _, d in got[len(want):]), "extra parameters must be defaulted"
+
+    for n, want in gold["fake_quant"].items():
+        check(getattr(fq, n), want)
+    check(fq.W4A4Linear.__init__, gold["W4A4Linear.__init__"])
+    check(fq.W4A4Linear.from_float, gold["W4A4Linear.from_float"])
+    for n, want in gold["smooth"].items():
+        check(getattr(sm, n), want)
+
+
+def test_drop_in_import_paths():
+    import smoothquant
+    from smoothquant import quantize_model, smooth_lm                    # smoothquant/__init__.py:1-4
+    from smoothquant.fake_quant import W4A4Linear, quantize_llama_like, quantize_opt  # run_experiments.py:21
+    from smoothquant.smooth import smooth_lm as s2                       # ppl_eval.py:4
+    assert smooth_lm is s2 and callable(quantize_model) and smoothquant.__all__ == ["smooth_lm", "quantize_model"]
+    assert W4A4Linear.__name__ == "W4A4Linear" and callable(quantize_llama_like) and callable(quantize_opt)
+
+
+def test_no_cpu_fallback_and_python_side_errors():
+    from smoothquant_mixedprecision_b200 import fake_quant as fq, ops
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        ops.colstat(torch.zeros(4, 8))
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        fq.W4A4Linear.from_float(torch.nn.Linear(8, 8))
+    with pytest.raises(ValueError):
+        fq.W4A4Linear(8, 8, act_quant="per_row")
+    with pytest.raises(ValueError):
+        fq.W4A4Linear.from_float(torch.nn.Linear(8, 8), weight_quant="nope")
+    with pytest.raises(ValueError):
+        fq.quantize_model(torch.nn.Linear(2, 2))
+    m = fq.W4A4Linear(16, 8, importance=torch.arange(16.0), salient_prop=0.2)
+    assert m.salient_indices.tolist() == [15, 14, 13]                    # max(1, int(.2*16)) most important channels
+    assert "W4A4Linear(16, 8, bias=True" in repr(m)
+
+
+def test_product_code_never_imports_the_oracle():
+    pkg = os.path.join(ROOT, "smoothquant_mixedprecision_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".cpp", ".h")):
+                src = open(os.path.join(dirpath, f)).read()
+                assert "oracle" not in src, os.path.join(dirpath, f)

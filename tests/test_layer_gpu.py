@@ -1,0 +1,196 @@
+"""GPU parity of the module-swap API (W4A4Linear, walkers, smooth_lm) against reference-generated golden fixtures
+(tests/golden/make_golden.py) and the CPU oracle.  Fake-quantised operands are compared bit for bit; layer outputs
+and logits within the tolerance written next to each assertion."""
+import pytest
+import torch
+from torch import nn
+
+from oracle import mq_oracle as O
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+@pytest.fixture(scope="module")
+def fq():
+    from smoothquant_mixedprecision_b200 import fake_quant
+    return fake_quant
+
+
+def _linear_from(c):
+    lin = nn.Linear(c["K"], c["N"], bias=c["bias"] is not None)
+    with torch.no_grad():
+        lin.weight.copy_(c["weight_fp"])
+        if c["bias"] is not None:
+            lin.bias.copy_(c["bias"])
+    return lin.to(c["weight_fp"].dtype).to(DEV)
+
+
+def _replayed_perms(c):
+    """Column-id permutations the reference actually used (recorded through the argsort tap)."""
+    K = c["K"]
+    keep = O.nonsalient_columns(K, c["salient_indices"])
+    wperm = c["init_argsorts"][-1] if c["weight_quant"] == "per_group" else None
+    aperm = operm = None
+    if c["act_quant"] == "per_group":
+        aperm = keep[c["fwd_argsorts"][0]]
+        if c["quantize_output"]:
+            operm = keep[c["fwd_argsorts"][2]]
+    return wperm, aperm, operm
+
+
+def test_reference_mode_layer_matches_golden(fq, golden_layers):
+    for c in golden_layers:
+        wperm, aperm, operm = _replayed_perms(c)
+        p = c["salient_prop"]
+        mod = fq.W4A4Linear.from_float(_linear_from(c), weight_quant=c["weight_quant"], act_quant=c["act_quant"],
+                                       quantize_output=c["quantize_output"],
+                                       importance=c["importance"] if p > 0 else None, salient_prop=p, quant_bits=4,
+                                       group_size=c["group_size"], mode="reference",
+                                       weight_perm=None if wperm is None else wperm.to(DEV))
+        if c["salient_indices"] is None:
+            assert mod.salient_indices is None
+        else:
+            assert torch.equal(mod.salient_indices.cpu(), c["salient_indices"])      # fake_quant.py:265-270
+        assert torch.equal(mod.weight.cpu(), c["weight_q"])                          # fake_quant.py:347-365, bit-exact
+        assert repr(mod) == c["repr"]
+        x = c["x"].to(DEV)
+        y = mod(x.clone(), act_perm=None if aperm is None else aperm.to(DEV),
+                out_perm=None if operm is None else operm.to(DEV))
+        assert y.shape == c["y"].shape and y.dtype == c["y"].dtype
+        ref = c["y"].float()
+        err = (y.float().cpu() - ref)
+        # tolerance: fp16 (bf16) output rounding + accumulation order; fp32 modules run the GEMM on fp16 operands
+        rel = {torch.float16: 2e-3, torch.bfloat16: 1.6e-2, torch.float32: 4e-3}[c["x"].dtype]
+        if c["quantize_output"]:     # a 1-ulp change of y can move an output code by one step: compare in norm
+            assert float(err.norm() / ref.norm()) < 3e-2
+        else:
+            assert float(err.abs().max()) <= rel * float(ref.abs().max())
+
+
+def test_reference_mode_dynamic_sort_matches_oracle(fq, golden_layers):
+    """No replayed permutation: K0 -> K0b -> K1 on the device must reproduce the reference's q_x when the keys are
+    tie-free (canonical order == any order)."""
+    n = 0
+    for c in golden_layers:
+        if c["act_quant"] != "per_group":
+            continue
+        x2 = c["x"].reshape(-1, c["K"])
+        keep = O.nonsalient_columns(c["K"], c["salient_indices"])
+        key = O.sort_key(x2[:, keep], "max")
+        if key.unique().numel() != key.numel():
+            continue
+        n += 1
+        mod = fq.W4A4Linear.from_float(_linear_from(c), "per_group", "per_group", importance=c["importance"] if
+                                       c["salient_prop"] > 0 else None, salient_prop=c["salient_prop"],
+                                       group_size=c["group_size"])
+        got = mod._fake_quant_nonsalient(x2.to(DEV), "per_group").cpu()
+        _, want = O.w4a4_forward_reference(x2, c["weight_q"], None, c["salient_indices"], 4, c["group_size"],
+                                           return_qx=True)
+        assert torch.equal(got, want)
+    assert n >= 1
+
+
+@pytest.mark.parametrize("sort", ["max", "mean3std", "argmax", "none"])
+def test_fused_mode_layer_matches_composed_oracle(fq, golden_layers, sort):
+    for c in golden_layers:
+        if c["act_quant"] != "per_group" or c["quantize_output"]:
+            continue
+        K, g, p = c["K"], c["group_size"], c["salient_prop"]
+        x2 = c["x"].reshape(-1, K)
+        key = None if sort == "none" else O.sort_key(x2, sort).float()
+        mod = fq.W4A4Linear.from_float(_linear_from(c), "per_group", "per_group",
+                                       importance=c["importance"] if p > 0 else None, salient_prop=p, group_size=g,
+                                       mode="fused", sort=sort, sort_key=key)
+        part = O.fused_partition(K, c["salient_indices"], key, g)
+        xo, wo = x2, c["weight_fp"]
+        if xo.dtype == torch.float32:          # fused mode computes in fp16: the oracle sees the same cast
+            xo, wo = xo.half(), wo.half()
+        y64, aq, wq = O.fused_layer_oracle(xo, wo, c["bias"], part)
+        assert torch.equal(mod.perm.cpu().long(), part.perm)
+        G = aq.scales.shape[1]
+        assert torch.equal(mod.w_codes.cpu()[:, : G * g], wq.codes)                   # bit-exact codes
+        assert torch.equal(mod.w_scales.cpu()[:, : c["N"]].t(), wq.scales.float())    # bit-exact scales
+        y = mod(c["x"].to(DEV)).reshape(-1, c["N"]).double().cpu()
+        tol = (8e-3 if xo.dtype == torch.bfloat16 else 1e-3) * float(y64.abs().max()) + 1e-3
+        assert float((y - y64).abs().max()) <= tol
+        # API compatibility: the lazily dequantised weight equals the oracle's dequantised operand
+        wd = mod.weight.cpu()
+        want = torch.zeros_like(wo)
+        want[:, part.perm] = wq.deq
+        want[:, part.salient] = wo[:, part.salient]
+        assert torch.equal(wd, want)
+
+
+def test_error_behaviour_matches_reference(fq):
+    lin = nn.Linear(64, 32).half().to(DEV)
+    with pytest.raises(ValueError):
+        fq.W4A4Linear.from_float(lin, weight_quant="bogus")                           # fake_quant.py:361
+    with pytest.raises(ValueError):
+        fq.W4A4Linear(64, 32, act_quant="bogus")                                      # fake_quant.py:256
+    with pytest.raises(AssertionError):
+        fq.W4A4Linear.from_float(nn.ReLU())                                           # fake_quant.py:335
+    mod = fq.W4A4Linear.from_float(lin, "per_group", "per_group", group_size=32)
+    with pytest.raises(ValueError):
+        mod(torch.zeros(2, 2, 2, 64, dtype=torch.float16, device=DEV))                # fake_quant.py:287
+    imp = torch.rand(64)
+    mod = fq.W4A4Linear.from_float(lin, "per_group", "per_group", quantize_output=True, importance=imp,
+                                   salient_prop=0.1, group_size=32)
+    with pytest.raises(IndexError):                                                   # N != K, SURVEY F6
+        mod(torch.randn(4, 64, dtype=torch.float16, device=DEV))
+
+
+def _build(kind, cfgd):
+    from transformers import LlamaConfig, LlamaForCausalLM, OPTConfig, OPTForCausalLM
+    if kind == "llama":
+        return LlamaForCausalLM(LlamaConfig(**{k: v for k, v in cfgd.items() if k in (
+            "vocab_size", "hidden_size", "intermediate_size", "num_hidden_layers", "num_attention_heads",
+            "num_key_value_heads", "max_position_embeddings")})).eval()
+    return OPTForCausalLM(OPTConfig(**{k: v for k, v in cfgd.items() if k in (
+        "vocab_size", "hidden_size", "ffn_dim", "num_hidden_layers", "num_attention_heads",
+        "max_position_embeddings", "word_embed_proj_dim")})).eval()
+
+
+@pytest.mark.parametrize("kind", ["llama", "opt"])
+def test_model_walkers_and_smooth_lm(fq, golden_models, kind):
+    from smoothquant_mixedprecision_b200.smooth import smooth_lm
+    c = golden_models[kind]
+    model = _build(kind, c["config"])
+    model.load_state_dict(c["state0"])
+    smooth_lm(model, c["act_scales"], c["alpha"])                                      # on CPU: bit-identical
+    for k, v in model.state_dict().items():
+        assert torch.equal(v, c["state_smoothed"][k]), k
+    model = model.to(DEV)
+    walker = fq.quantize_model if kind == "llama" else fq.quantize_opt
+    walker(model, weight_quant="per_group", act_quant="per_group", input_feat=c["input_feat"],
+           salient_prop=c["salient_prop"], group_size=c["group_size"])
+    mods = {n: m for n, m in model.named_modules() if isinstance(m, fq.W4A4Linear)}
+    assert set(mods) == set(c["quant_weights"])
+    assert not isinstance(model.lm_head, fq.W4A4Linear)
+    exact = 0
+    for n, m in mods.items():
+        assert torch.equal(torch.sort(m.salient_indices.cpu()).values, torch.sort(c["salient"][n]).values), n
+        exact += int(torch.equal(m.weight.cpu(), c["quant_weights"][n]))
+    # weight column maxima of fp32 random-init layers are tie-free -> every packed weight is bit-exact
+    assert exact == len(mods)
+    with torch.no_grad():
+        logits = model(c["ids"].to(DEV)).logits.float().cpu()
+    ref = c["logits_w4a4"].float()
+    rel = float((logits - ref).norm() / ref.norm())
+    # fp32 reference vs fp16-operand GEMMs, dynamic re-sorting per call and (OPT) output quantisation in between:
+    # relative L2 error of the logits below 5 %, and agreement of the arg-max token wherever the reference's
+    # top-1 margin exceeds that error level
+    assert rel < 5e-2, rel
+    top2 = ref.topk(2, dim=-1).values
+    sure = (top2[..., 0] - top2[..., 1]) > 4 * (logits - ref).abs().max()
+    assert torch.equal(logits.argmax(-1)[sure], ref.argmax(-1)[sure])
+
+
+def test_quantize_model_error_and_key_behaviour(fq):
+    from transformers import OPTConfig, OPTForCausalLM
+    with pytest.raises(ValueError):
+        fq.quantize_model(nn.Linear(4, 4))                                             # fake_quant.py:799
+    m = OPTForCausalLM(OPTConfig(vocab_size=64, hidden_size=32, ffn_dim=64, num_hidden_layers=1,
+                                 num_attention_heads=2, max_position_embeddings=32, word_embed_proj_dim=32)).to(DEV)
+    with pytest.raises(KeyError):                                                      # no guard in quantize_opt (:396)
+        fq.quantize_opt(m, "per_group", "per_group", input_feat={}, salient_prop=0.05)
