@@ -1,0 +1,304 @@
+"""Benchmark of the W4A4 MixedQuant linear hot path (BASELINE.json config 3).
+
+Workload (one "step"): every W4A4 linear of Llama-2-7B (32 decoder layers x {q,k,v,o,gate,up,down} = 224 layers,
+group 128, 5 % salient FP16 channels, static max-sort permutation, mode="fused") applied to one batch of 16 x 2048 =
+32 768 tokens per GPU, chained through their real shapes (x -> q,k,v ; v -> o ; o -> gate,up ; up -> down -> next
+layer).  Attention / norms / lm_head are not part of the path and are not executed.  Synthetic fp16 activations and
+random-init weights.  N > 1: one replica per GPU, data-parallel over sequences, no data-path collective ("weak").
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+
+`value`   tokens/s with inputs resident in HBM (CUDA events, max over ranks)
+`e2e`     the same through the module API with HOST buffers: pinned host activations -> device, the 224 layers,
+          last output -> host, all inside the timed region
+`roofline` of the dominant kernel (mixed GEMM), CUDA events around every launch inside the timed region
+`cpu_baseline` the CPU oracle port of the reference layer on a bounded sample (rank 0, N = 1 only)
+`--impl reference` times that CPU path alone (all host threads) and prints the same line with "impl": "reference".
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+HIDDEN, INTER, LAYERS = 4096, 11008, 32
+GROUP, SALIENT = 128, 0.05
+SHAPES = {"q_proj": (HIDDEN, HIDDEN), "k_proj": (HIDDEN, HIDDEN), "v_proj": (HIDDEN, HIDDEN),
+          "o_proj": (HIDDEN, HIDDEN), "gate_proj": (INTER, HIDDEN), "up_proj": (INTER, HIDDEN),
+          "down_proj": (HIDDEN, INTER)}           # name -> (N, K)
+METRIC = "llama2_7b_w4a4_linear_prefill_tokens_per_s"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--tokens", type=int, default=16 * 2048, help="tokens per GPU per step")
+    ap.add_argument("--layers", type=int, default=LAYERS)
+    ap.add_argument("--cpu-tokens", type=int, default=1024, help="tokens of the bounded CPU sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def ops_per_token(layers):
+    return 2.0 * layers * sum(n * k for n, k in SHAPES.values())
+
+
+# ---------------------------------------------------------------------------------------------- CPU arm (oracle)
+def cpu_layer_sample(tokens, threads):
+    """One decoder layer's 7 linears through the oracle's literal reference layer (fp32, like the reference's own CPU
+    runs, examples/group_size_analysis.py:62-66).  Returns a closure running one pass and the setup seconds."""
+    import torch
+    from oracle import mq_oracle as O
+    torch.set_num_threads(threads)
+    g = torch.Generator().manual_seed(0)
+    t0 = time.perf_counter()
+    layers = {}
+    xs = {K: torch.randn(tokens, K, generator=g) * torch.exp(0.5 * torch.randn(K, generator=g))
+          for K in (HIDDEN, INTER)}
+    for name, (N, K) in SHAPES.items():
+        w = torch.randn(N, K, generator=g) / K ** 0.5
+        imp = xs[K].abs().mean(dim=0)
+        sal = O.select_salient(imp, SALIENT)
+        layers[name] = (O.w4a4_weight_reference(w, sal, 4, GROUP), sal, K)
+    setup = time.perf_counter() - t0
+
+    def run():
+        out = None
+        for name, (wq, sal, K) in layers.items():
+            out = O.w4a4_forward_reference(xs[K], wq, None, sal, 4, GROUP)
+        return out
+    return run, setup
+
+
+def time_cpu(tokens, steps, warmup):
+    import torch
+    threads = os.cpu_count() or 1
+    run, setup = cpu_layer_sample(tokens, threads)
+    for _ in range(warmup):
+        run()
+    ts = []
+    for _ in range(steps):
+        t0 = time.perf_counter()
+        run()
+        ts.append(time.perf_counter() - t0)
+    per_layer = sum(ts) / len(ts)
+    return {"tok_s": tokens / (per_layer * LAYERS), "s_per_layer": per_layer, "threads": threads, "setup_s": setup,
+            "sample": f"1 of {LAYERS} decoder layers (7 linears), {tokens} tokens, fp32, oracle port of "
+                      f"W4A4Linear.forward; tokens/s = tokens / (t_layer * {LAYERS})",
+            "torch_threads": torch.get_num_threads()}
+
+
+def reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    r = time_cpu(args.cpu_tokens, max(1, args.steps), max(0, args.warmup))
+    line = {"impl": "reference", "metric": METRIC, "value": r["tok_s"], "unit": "tokens/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["s_per_layer"] * LAYERS * 1e3 *
+            (args.tokens / args.cpu_tokens), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "Llama-2-7B W4A4 linears g=128 5% salient, CPU fake-quant path", "tokens_per_step":
+                       args.tokens, "group_size": GROUP, "salient_prop": SALIENT},
+            "cpu_baseline": {"value": r["tok_s"], "unit": "tokens/s", "cores": r["threads"], "kind": "port",
+                             "sample": r["sample"]},
+            "e2e": {"value": r["tok_s"], "unit": "tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+# ---------------------------------------------------------------------------------------------- GPU arm
+class ClockSampler:
+    """nvidia-smi sampling of SM clocks / throttle reasons during the timed region (B200_PROFILING.md)."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.p = None
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(index), f"--query-gpu={self.Q}",
+                                       "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
+                                      stderr=subprocess.DEVNULL, text=True)
+        except OSError:
+            pass
+
+    def stop(self):
+        if self.p is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.p.terminate()
+        try:
+            out = self.p.communicate(timeout=5)[0]
+        except subprocess.TimeoutExpired:
+            self.p.kill()
+            out = ""
+        clocks, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in out.splitlines():
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 6 or not f[0].isdigit():
+                continue
+            clocks.append(int(f[0]))
+            mx = int(f[1])
+            for n, v in zip(names, f[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        busy = [c for c in clocks if mx and c > 0.3 * mx] or clocks
+        return {"sm_mhz": statistics.median(busy) if busy else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
+                "samples": len(clocks)}
+
+
+def build_stack(layers, tokens, dev, seed):
+    """Random-init Llama-2-7B linears packed for mode="fused" (P0 on the GPU) + synthetic calibration statistics."""
+    import torch
+    from smoothquant_mixedprecision_b200.fake_quant import W4A4Linear
+    g = torch.Generator(device=dev).manual_seed(seed)
+    chan = {K: torch.exp(0.5 * torch.randn(K, device=dev, generator=g)) for K in (HIDDEN, INTER)}
+    stack = []
+    for _ in range(layers):
+        mods = {}
+        for name, (N, K) in SHAPES.items():
+            lin = torch.nn.Linear(K, N, bias=False, device=dev, dtype=torch.float16)
+            with torch.no_grad():
+                lin.weight.copy_(torch.randn(N, K, device=dev, generator=g) / K ** 0.5)
+            # synthetic calibration: importance = mean|x| (run_experiments.py:60), sort key = max|x| (calibration.py:18-25)
+            imp = chan[K] * (1 + 0.05 * torch.rand(K, device=dev, generator=g))
+            mods[name] = W4A4Linear.from_float(lin, "per_group", "per_group", importance=imp.cpu(),
+                                               salient_prop=SALIENT, group_size=GROUP, mode="fused",
+                                               sort_key=imp * 4.0)
+            del lin
+        stack.append(mods)
+    x0 = (torch.randn(tokens, HIDDEN, device=dev, generator=g) * chan[HIDDEN]).half()
+    return stack, x0
+
+
+def run_stack(stack, x):
+    for m in stack:
+        m["q_proj"](x)
+        m["k_proj"](x)
+        v = m["v_proj"](x)
+        o = m["o_proj"](v)
+        m["gate_proj"](o)
+        u = m["up_proj"](o)
+        x = m["down_proj"](u)
+    return x
+
+
+def gpu_arm(args):
+    import torch
+    import torch.distributed as dist
+    from smoothquant_mixedprecision_b200 import ops, _lib
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (the product path has no CPU fallback)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    M = args.tokens
+    stack, x0 = build_stack(args.layers, M, dev, seed=1234 + rank)
+    hx = torch.empty(x0.shape, dtype=x0.dtype, pin_memory=True).copy_(x0)
+    hy = torch.empty(x0.shape, dtype=x0.dtype, pin_memory=True)
+    xd = torch.empty_like(x0)
+
+    def sync_all():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        sync_all()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        sync_all()
+        t = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item()) / steps
+
+    def step_resident():
+        run_stack(stack, x0)
+
+    def step_e2e():
+        xd.copy_(hx, non_blocking=True)
+        y = run_stack(stack, xd)
+        hy.copy_(y, non_blocking=True)
+        torch.cuda.current_stream().synchronize()      # the caller holds the result on the host
+
+    for _ in range(max(3, args.warmup)):
+        step_resident()
+    c0 = ops.COUNTERS["launch_calls"]
+    ops.GEMM_EVENTS = []
+    sampler = ClockSampler(local) if rank == 0 else None
+    ms = timed(step_resident, args.steps)
+    clocks = sampler.stop() if sampler else None
+    launches = (ops.COUNTERS["launch_calls"] - c0) // args.steps
+    ev, ops.GEMM_EVENTS = ops.GEMM_EVENTS, None
+    gemm_ms = sum(a.elapsed_time(b) for a, b, _, _ in ev) / args.steps
+    ops_i8 = sum(e[2] for e in ev) / args.steps
+    ops_f16 = sum(e[3] for e in ev) / args.steps
+    step_e2e()
+    ms_e2e = timed(step_e2e, args.steps)
+    fault = _lib.gemm_fault()[0] or _lib.quant_fault()[0]
+    if fault:
+        raise SystemExit(f"bench.py: kernel fault record {fault:#x}")
+    if rank != 0:
+        return
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except OSError:
+        pass
+    bf16 = peaks.get("bf16_tflops_sustained") or 1400.0          # fallback: B200_PROFILING.md sustained figure
+    peak_src = "measured (MEASURED_PEAKS.json bf16_tflops_sustained; int8 taken as 2x)" if peaks else \
+        "fallback 1.4 PF bf16 sustained; int8 taken as 2x"
+    t_roof_ms = (ops_i8 / (2 * bf16 * 1e12) + ops_f16 / (bf16 * 1e12)) * 1e3
+    achieved = (ops_i8 + ops_f16) / (gemm_ms * 1e-3) / 1e12
+    peak_mix = (ops_i8 + ops_f16) / (t_roof_ms * 1e-3) / 1e12
+    line = {"metric": METRIC, "value": world * M / (ms * 1e-3), "unit": "tokens/s", "n_gpus": world,
+            "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": ms, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "s8 codes (int32 accumulate) + f16 salient",
+            "data": "synthetic",
+            "config": {"workload": "Llama-2-7B W4A4 linears (224 layers), g=128, 5% salient FP16, static max-sort, "
+                                   "prefill 16x2048 tokens per GPU", "tokens_per_gpu": M, "layers": args.layers,
+                       "group_size": GROUP, "salient_prop": SALIENT, "parallelism": f"dp{world}",
+                       "l2": "inputs (268 MB activations, 6.9 GB weights) exceed the 126 MB L2; no flush"},
+            "tops": world * M * ops_per_token(args.layers) / (ms * 1e-3) / 1e12,
+            "e2e": {"value": world * M / (ms_e2e * 1e-3), "unit": "tokens/s", "h2d_bytes_per_step": hx.numel() * 2,
+                    "d2h_bytes_per_step": hy.numel() * 2, "ms_per_step": ms_e2e},
+            "gpu_launches": launches,
+            "roofline": {"kernel": "mixed_gemm_kernel", "bound": "tensor", "achieved": achieved, "peak": peak_mix,
+                         "unit": "TOP/s", "frac": achieved / peak_mix, "traffic": None, "peak_source": peak_src,
+                         "share_of_step": gemm_ms / ms, "launches_per_step": len(ev) // args.steps},
+            "clocks": clocks}
+    if world == 1 and not args.no_cpu_baseline:
+        r = time_cpu(args.cpu_tokens, 2, 1)
+        line["cpu_baseline"] = {"value": r["tok_s"], "unit": "tokens/s", "cores": r["threads"], "kind": "port",
+                                "sample": r["sample"]}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        reference_arm(args)
+    else:
+        gpu_arm(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -11,11 +11,22 @@ from typing import Optional
 import torch
 
 from . import _lib
-from ._lib import lib, check
+from ._lib import lib, check as _check
 
 _DTYPES = {torch.float16: _lib.MQ_F16, torch.bfloat16: _lib.MQ_BF16, torch.float32: _lib.MQ_F32}
 STAT_KINDS = {"max": _lib.MQ_STAT_ABSMAX, "absmax": _lib.MQ_STAT_ABSMAX, "mean": _lib.MQ_STAT_ABSMEAN,
               "absmean": _lib.MQ_STAT_ABSMEAN, "mean3std": _lib.MQ_STAT_MEAN3STD, "argmax": _lib.MQ_STAT_ARGMAX}
+
+
+# instrumentation for bench.py: number of kernel-launching C-ABI calls, and (optionally) CUDA-event pairs around every
+# mixed GEMM launch on the launching stream.  Neither synchronises.
+COUNTERS = {"launch_calls": 0}
+GEMM_EVENTS = None          # set to a list to collect (start_event, end_event, ops_int8, ops_f16)
+
+
+def check(rc: int, what: str = "") -> None:
+    COUNTERS["launch_calls"] += 1
+    _check(rc, what)
 
 
 def _round_up(v: int, m: int) -> int:
@@ -235,6 +246,10 @@ def mixed_gemm(a: Optional[QuantizedRows], w: Optional[QuantizedRows], bias: Opt
     if bias is not None:
         bias = bias.reshape(-1).to(device=dev, dtype=dt).contiguous()
     y = torch.empty((M, _round_up(N, 8)), dtype=dt, device=dev)
+    ev = None
+    if GEMM_EVENTS is not None:
+        ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+        ev[0].record(torch.cuda.current_stream(dev))
     with torch.cuda.device(dev):
         check(lib.mq_mixed_gemm(
             _ptr(a.codes) if G else None, a.codes.stride(0) if G else 0,
@@ -245,4 +260,7 @@ def mixed_gemm(a: Optional[QuantizedRows], w: Optional[QuantizedRows], bias: Opt
             _ptr(w_sal) if Ks else None, w_sal.stride(0) if Ks else 0,
             _ptr(bias), M, N, G, g, Ks, _DTYPES[dt], y.data_ptr(), y.stride(0), None, 0,
             torch.cuda.current_stream(dev).cuda_stream), "mq_mixed_gemm")
+    if ev is not None:
+        ev[1].record(torch.cuda.current_stream(dev))
+        GEMM_EVENTS.append((ev[0], ev[1], 2.0 * M * N * G * g, 2.0 * M * N * Ks))
     return y[:, :N]
