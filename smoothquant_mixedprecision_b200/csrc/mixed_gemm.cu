@@ -8,17 +8,20 @@
 // where q_x / self.weight hold dequantised code*scale values in the non-salient columns and FP16 originals in the
 // salient ones (fake_quant.py:291-301, :347-365).
 //
-// One CTA computes a 128 x BN tile of y.  Warp roles:
+// Persistent kernel: gridDim.x = min(#tiles, #SMs) CTAs of 384 threads, each looping over 128 x BN output tiles
+// (tile = blockIdx.x + i * gridDim.x; n-block fastest so that concurrently running CTAs share A rows in L2).
 //   warp 0      TMA producer: 128-byte-wide K blocks of A (128 rows) and W (BN rows) into a kStages ring
-//               (SWIZZLE_128B, one mbarrier pair per stage)
-//   warp 1      MMA issuer (one thread): per K group g it issues g/32 tcgen05.mma.kind::i8 (M=128, N=BN, K=32)
-//               into one of two TMEM accumulator stages (int32), commits the stage to the epilogue, moves on to
-//               the other stage; the salient slice is the last "group", issued as kind::f16 (fp32 accumulator)
-//   warp 2      TMEM allocation / deallocation (2*BN columns)
-//   warps 4..   epilogue: thread t of a warp owns TMEM lane (= tile row) 32*(warp%4)+t and CW columns; after each
-//               group it reads the int32 partial sums with tcgen05.ld, converts, multiplies by
-//               a_scale[g,m]*w_scale[g,n] and accumulates in fp32 registers, releases the TMEM stage, and at the
-//               end adds the bias, rounds to fp16/bf16 and stores the row segment.
+//               (SWIZZLE_128B, one full/empty mbarrier pair per stage)
+//   warp 1      MMA issuer (one thread): per accumulation unit (a K group of codes, or the salient slice) it issues
+//               tcgen05.mma kind::i8 / kind::f16 (M=128, N=BN, K=32 bytes) into one of two TMEM accumulator stages,
+//               commits the stage to the epilogue and moves on to the other stage
+//   warp 2      TMEM allocation / deallocation (2*BN columns);  warp 3 idle
+//   warps 4-11  epilogue (two warpgroups, registers raised with setmaxnreg): thread t of a warp owns TMEM lane
+//               (= tile row) 32*(warp%4)+t and BN/2 columns.  Per unit it reads the int32 partial sums with
+//               tcgen05.ld, converts them with the 2^23 magic-number trick (|sum| <= g*49 << 2^22, exact), scales by
+//               a_scale[g,m]*w_scale[g,n] with packed f32x2 math and accumulates in fp32 registers; it releases the
+//               TMEM stage as soon as its loads have completed, so the MMAs of the next unit (and of the next tile,
+//               while this tile's output is being rounded and stored) overlap the rescale.
 #include <cuda.h>
 
 #include "common.cuh"
@@ -31,6 +34,8 @@ using namespace mqptx;
 constexpr int BM = 128;
 constexpr int kKBlockBytes = 128;  // one swizzle atom wide
 constexpr int kFirstEpiWarp = 4;
+constexpr int kEpiWarps = 8;
+constexpr int kThreads = (kFirstEpiWarp + kEpiWarps) * 32;
 
 struct GemmArgs {
   const float* a_scales;
@@ -43,6 +48,8 @@ struct GemmArgs {
   int M, N, G, g;
   int kb_int;  // 128-column K blocks of codes holding the G*g quantised columns
   int kb_sal;  // 64-column K blocks of the salient slice
+  int tiles_m, tiles_n;
+  int debug;  // bit 0: epilogue skips the rescale math; bit 1: MMA warp issues no MMAs (timing experiments only)
 };
 
 template <int BN, int kStages>
@@ -56,15 +63,24 @@ struct SmemLayout {
   static constexpr int kTotal = kBarOffset + kBarBytes + 1024;  // + slack to align the base to 1024 bytes
 };
 
-template <typename OutT, int BN, int CW, int kStages>
-__global__ void __launch_bounds__((kFirstEpiWarp + 4 * BN / CW) * 32, 1)
+template <int kRegs>
+__device__ __forceinline__ void reg_dealloc() {
+  asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kRegs));
+}
+template <int kRegs>
+__device__ __forceinline__ void reg_alloc() {
+  asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(kRegs));
+}
+
+template <typename OutT, int BN, int kStages>
+__global__ void __launch_bounds__(kThreads, 1)
 mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_w,
                   const __grid_constant__ CUtensorMap map_as, const __grid_constant__ CUtensorMap map_ws,
                   const GemmArgs p) {
   using L = SmemLayout<BN, kStages>;
-  constexpr int kEpiWarps = 4 * BN / CW;
+  constexpr int CW = BN / 2;  // columns per epilogue thread
   constexpr int kTmemCols = 2 * BN;
-  static_assert(BN % CW == 0 && CW % 32 == 0, "bad epilogue split");
+  static_assert(CW % 32 == 0, "bad epilogue split");
   static_assert(kTmemCols == 256 || kTmemCols == 512 || kTmemCols == 128, "TMEM columns must be a power of two");
 
   extern __shared__ unsigned char smem_raw[];
@@ -78,9 +94,9 @@ mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int n0 = blockIdx.x * BN, m0 = blockIdx.y * BM;
-  const int units = p.G + (p.kb_sal > 0 ? 1 : 0);  // accumulation units: K groups, then the salient slice
+  const int units = p.G + (p.kb_sal > 0 ? 1 : 0);  // accumulation units per tile: K groups, then the salient slice
   const int kb_total = p.kb_int + p.kb_sal;
+  const int num_tiles = p.tiles_m * p.tiles_n;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&map_a);
@@ -105,146 +121,166 @@ mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
   tc_fence_after();
   const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(tmem_slot);
 
-  if (warp == 0) {
-    // ------------------------------------------------------------------ TMA producer
-    if (lane == 0) {
-      for (int kb = 0; kb < kb_total; ++kb) {
-        const int s = kb % kStages;
-        const uint32_t ph = (uint32_t)(kb / kStages) & 1u;
-        if (!mbar_wait(&empty_bar[s], ph ^ 1u, 0x200u + s)) break;
-        unsigned char* sa = smem + (size_t)s * L::kStageBytes;
-        unsigned char* sb = sa + L::kABytes;
-        mbar_expect_tx(&full_bar[s], (uint32_t)L::kStageBytes);
-        if (kb < p.kb_int) {
-          tma_load_2d(sa, &map_a, kb * 128, m0, &full_bar[s]);
-          tma_load_2d(sb, &map_w, kb * 128, n0, &full_bar[s]);
-        } else {
-          const int ks = (kb - p.kb_int) * 64;
-          tma_load_2d(sa, &map_as, ks, m0, &full_bar[s]);
-          tma_load_2d(sb, &map_ws, ks, n0, &full_bar[s]);
+  if (warp < kFirstEpiWarp) {
+    reg_dealloc<40>();
+    if (warp == 0 && lane == 0) {
+      // ------------------------------------------------------------------ TMA producer
+      uint32_t kbc = 0;  // K blocks issued so far (ring position)
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const int m0 = (tile / p.tiles_n) * BM, n0 = (tile % p.tiles_n) * BN;
+        for (int kb = 0; kb < kb_total; ++kb, ++kbc) {
+          const uint32_t s = kbc % kStages, ph = (kbc / kStages) & 1u;
+          if (!mbar_wait(&empty_bar[s], ph ^ 1u, 0x200u + s)) goto teardown;
+          unsigned char* sa = smem + (size_t)s * L::kStageBytes;
+          unsigned char* sb = sa + L::kABytes;
+          mbar_expect_tx(&full_bar[s], (uint32_t)L::kStageBytes);
+          if (kb < p.kb_int) {
+            tma_load_2d(sa, &map_a, kb * 128, m0, &full_bar[s]);
+            tma_load_2d(sb, &map_w, kb * 128, n0, &full_bar[s]);
+          } else {
+            const int ks = (kb - p.kb_int) * 64;
+            tma_load_2d(sa, &map_as, ks, m0, &full_bar[s]);
+            tma_load_2d(sb, &map_ws, ks, n0, &full_bar[s]);
+          }
         }
       }
-    }
-  } else if (warp == 1) {
-    // ------------------------------------------------------------------ MMA issuer
-    if (lane == 0) {
+    } else if (warp == 1 && lane == 0) {
+      // ------------------------------------------------------------------ MMA issuer
       constexpr uint32_t idesc_i8 = umma_idesc(2u, 1u, BM, BN);
-      const uint32_t idesc_f16 = umma_idesc(1u, sizeof(OutT) == 2 && Num<OutT>::kDtype == MQ_BF16 ? 1u : 0u, BM, BN);
+      const uint32_t idesc_f16 = umma_idesc(1u, Num<OutT>::kDtype == MQ_BF16 ? 1u : 0u, BM, BN);
       const int mma_per_group = p.g / 32;
-      int kb = 0;        // K block currently being consumed
-      int sub = 0;       // next 32-byte slice inside the K block (0..3)
-      bool ok = true;
-      for (int u = 0; u < units && ok; ++u) {
-        const int t = u & 1;
-        if (!mbar_wait(&tempty_bar[t], ((uint32_t)(u >> 1) & 1u) ^ 1u, 0x300u + t)) break;
-        tc_fence_after();
-        const uint32_t d_tmem = tmem_base + (uint32_t)(t * BN);
-        const bool is_sal = u >= p.G;
-        if (is_sal && sub != 0) {  // codes end in the middle of a K block (zero padding): release it
-          tc_commit(&empty_bar[kb % kStages]);
-          ++kb;
-          sub = 0;
-        }
-        const int n_mma = is_sal ? p.kb_sal * 4 : mma_per_group;
-        for (int i = 0; i < n_mma; ++i) {
-          const int s = kb % kStages;
-          if (sub == 0) {
-            if (!mbar_wait(&full_bar[s], (uint32_t)(kb / kStages) & 1u, 0x400u + s)) {
-              ok = false;
-              break;
+      uint32_t kbc = 0, uc = 0;  // K blocks consumed, units issued (ring positions)
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        int sub = 0;  // next 32-byte slice inside the current K block (0..3)
+        for (int u = 0; u < units; ++u, ++uc) {
+          const uint32_t t = uc & 1u;
+          if (!mbar_wait(&tempty_bar[t], ((uc >> 1) & 1u) ^ 1u, 0x300u + t)) goto teardown;
+          tc_fence_after();
+          const uint32_t d_tmem = tmem_base + t * BN;
+          const bool is_sal = u >= p.G;
+          const int n_mma = is_sal ? p.kb_sal * 4 : mma_per_group;
+          for (int i = 0; i < n_mma; ++i) {
+            const uint32_t s = kbc % kStages;
+            if (sub == 0) {
+              if (!mbar_wait(&full_bar[s], (kbc / kStages) & 1u, 0x400u + s)) goto teardown;
+              tc_fence_after();
             }
-            tc_fence_after();
+            const uint32_t sa = smem_u32(smem + (size_t)s * L::kStageBytes);
+            const uint64_t da = umma_desc_k128(sa) + (uint64_t)(sub * 2);
+            const uint64_t db = umma_desc_k128(sa + L::kABytes) + (uint64_t)(sub * 2);
+            if (p.debug & 2) {
+            } else if (is_sal)
+              mma_f16_ss(d_tmem, da, db, idesc_f16, i > 0 ? 1u : 0u);
+            else
+              mma_i8_ss(d_tmem, da, db, idesc_i8, i > 0 ? 1u : 0u);
+            if (++sub == 4) {
+              tc_commit(&empty_bar[s]);  // smem stage free once these MMAs have read it
+              ++kbc;
+              sub = 0;
+            }
           }
-          const uint32_t sa = smem_u32(smem + (size_t)s * L::kStageBytes);
-          const uint64_t da = umma_desc_k128(sa) + (uint64_t)(sub * 2);
-          const uint64_t db = umma_desc_k128(sa + L::kABytes) + (uint64_t)(sub * 2);
-          if (is_sal)
-            mma_f16_ss(d_tmem, da, db, idesc_f16, i > 0 ? 1u : 0u);
-          else
-            mma_i8_ss(d_tmem, da, db, idesc_i8, i > 0 ? 1u : 0u);
-          if (++sub == 4) {
-            tc_commit(&empty_bar[s]);  // smem stage free once these MMAs have read it
-            ++kb;
+          if (u == p.G - 1 && sub != 0) {  // codes end inside a K block (zero padding): release it
+            tc_commit(&empty_bar[kbc % kStages]);
+            ++kbc;
             sub = 0;
           }
+          tc_commit(&tfull_bar[t]);  // accumulator stage t complete -> epilogue
         }
-        if (!ok) break;
-        tc_commit(&tfull_bar[t]);  // accumulator stage t complete -> epilogue
       }
     }
-  } else if (warp >= kFirstEpiWarp) {
-    // ------------------------------------------------------------------ epilogue
+  } else {
+    // ------------------------------------------------------------------ epilogue (warps 4..11)
+    reg_alloc<232>();
     const int ew = warp - kFirstEpiWarp;
-    const int quarter = warp & 3;                  // TMEM lane quarter this warp may access
-    const int col0 = (ew / 4) * CW;                // first tile column owned by this thread
-    const int m = m0 + quarter * 32 + lane;
-    const bool row_ok = m < p.M;
-    float acc[CW];
+    const int quarter = warp & 3;      // TMEM lane quarter this warp may access
+    const int col0 = (ew >> 2) * CW;   // first tile column owned by this thread
+    constexpr float kMagic = 12582912.0f;  // 1.5 * 2^23: int32 v (|v| < 2^22) + bits(kMagic) == bits(kMagic + v)
+    const float2 neg_magic = make_float2(-kMagic, -kMagic);
+    uint32_t uc = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      const int m0 = (tile / p.tiles_n) * BM, n0 = (tile % p.tiles_n) * BN;
+      const int m = m0 + quarter * 32 + lane;
+      const bool row_ok = m < p.M;
+      float2 acc[CW / 2];
 #pragma unroll
-    for (int j = 0; j < CW; ++j) acc[j] = 0.f;
+      for (int j = 0; j < CW / 2; ++j) acc[j] = make_float2(0.f, 0.f);
 
-    bool ok = true;
-    for (int u = 0; u < units && ok; ++u) {
-      const int t = u & 1;
-      const bool is_sal = u >= p.G;
-      float as = 1.f;
-      if (!is_sal) as = row_ok ? __ldg(p.a_scales + (int64_t)u * p.ld_as + m) : 0.f;
-      const float* wsp = p.w_scales + (int64_t)u * p.ld_ws + n0 + col0;
-      if (!mbar_wait(&tfull_bar[t], (uint32_t)(u >> 1) & 1u, 0x500u + t)) {
-        ok = false;
-        break;
-      }
-      tc_fence_after();
-      const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(t * BN + col0);
+      for (int u = 0; u < units; ++u, ++uc) {
+        const uint32_t t = uc & 1u;
+        const bool is_sal = u >= p.G;
+        float as = 1.f;
+        if (!is_sal) as = row_ok ? __ldg(p.a_scales + (int64_t)u * p.ld_as + m) : 0.f;
+        const float2 as2 = make_float2(as, as);
+        const float* wsp = p.w_scales + (int64_t)(is_sal ? 0 : u) * p.ld_ws + n0 + col0;
+        if (!mbar_wait(&tfull_bar[t], (uc >> 1) & 1u, 0x500u + t)) goto teardown;
+        tc_fence_after();
+        const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + t * BN + (uint32_t)col0;
+        uint32_t v[2][16];
+        tmem_ld_32x16(taddr, v[0]);
 #pragma unroll
-      for (int c = 0; c < CW / 32; ++c) {
-        uint32_t v[32];
-        tmem_ld_32x32(taddr + (uint32_t)(c * 32), v);
-        tmem_ld_wait();
-        if (is_sal) {
+        for (int c = 0; c < CW / 16; ++c) {
+          tmem_ld_wait();
+          if (c + 1 < CW / 16) tmem_ld_32x16(taddr + (uint32_t)((c + 1) * 16), v[(c + 1) & 1]);
+          if (c + 1 == CW / 16) {  // every load of this thread has landed: hand the TMEM stage back to the MMA warp
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&tempty_bar[t]);
+          }
+          const uint32_t* vv = v[c & 1];
+          if (p.debug & 1) {
+            acc[c * 8].x += __uint_as_float(vv[0]);
+          } else if (is_sal) {
 #pragma unroll
-          for (int j = 0; j < 32; ++j) acc[c * 32 + j] += __uint_as_float(v[j]);
-        } else {
+            for (int j = 0; j < 8; ++j)
+              acc[c * 8 + j] = __fadd2_rn(acc[c * 8 + j], make_float2(__uint_as_float(vv[2 * j]),
+                                                                      __uint_as_float(vv[2 * j + 1])));
+          } else {
 #pragma unroll
-          for (int j4 = 0; j4 < 8; ++j4) {
-            float4 ws = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (n0 + col0 + c * 32 + j4 * 4 < p.N) ws = __ldg(reinterpret_cast<const float4*>(wsp + c * 32 + j4 * 4));
-            acc[c * 32 + j4 * 4 + 0] = fmaf((float)(int)v[j4 * 4 + 0], as * ws.x, acc[c * 32 + j4 * 4 + 0]);
-            acc[c * 32 + j4 * 4 + 1] = fmaf((float)(int)v[j4 * 4 + 1], as * ws.y, acc[c * 32 + j4 * 4 + 1]);
-            acc[c * 32 + j4 * 4 + 2] = fmaf((float)(int)v[j4 * 4 + 2], as * ws.z, acc[c * 32 + j4 * 4 + 2]);
-            acc[c * 32 + j4 * 4 + 3] = fmaf((float)(int)v[j4 * 4 + 3], as * ws.w, acc[c * 32 + j4 * 4 + 3]);
+            for (int j4 = 0; j4 < 4; ++j4) {
+              float4 ws = make_float4(0.f, 0.f, 0.f, 0.f);
+              if (n0 + col0 + c * 16 + j4 * 4 < p.N) ws = __ldg(reinterpret_cast<const float4*>(wsp + c * 16 + j4 * 4));
+              float2 f0 = make_float2(__uint_as_float(vv[j4 * 4 + 0] + 0x4B400000u),
+                                      __uint_as_float(vv[j4 * 4 + 1] + 0x4B400000u));
+              float2 f1 = make_float2(__uint_as_float(vv[j4 * 4 + 2] + 0x4B400000u),
+                                      __uint_as_float(vv[j4 * 4 + 3] + 0x4B400000u));
+              f0 = __fadd2_rn(f0, neg_magic);
+              f1 = __fadd2_rn(f1, neg_magic);
+              const float2 s0 = __fmul2_rn(make_float2(ws.x, ws.y), as2);
+              const float2 s1 = __fmul2_rn(make_float2(ws.z, ws.w), as2);
+              acc[c * 8 + j4 * 2 + 0] = __ffma2_rn(f0, s0, acc[c * 8 + j4 * 2 + 0]);
+              acc[c * 8 + j4 * 2 + 1] = __ffma2_rn(f1, s1, acc[c * 8 + j4 * 2 + 1]);
+            }
           }
         }
       }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&tempty_bar[t]);
-    }
 
-    if (ok && row_ok) {
-      OutT* yrow = static_cast<OutT*>(p.y) + (int64_t)m * p.ldy + n0 + col0;
-      const OutT* bias = static_cast<const OutT*>(p.bias);
-      const bool vec_ok = (p.ldy % 8 == 0) && (reinterpret_cast<uintptr_t>(p.y) % 16 == 0);
+      if (row_ok) {  // bias, rounding, store of this thread's row segment (overlaps the next tile's first MMAs)
+        OutT* yrow = static_cast<OutT*>(p.y) + (int64_t)m * p.ldy + n0 + col0;
+        const OutT* bias = static_cast<const OutT*>(p.bias);
+        const bool vec_ok = (p.ldy % 8 == 0) && (reinterpret_cast<uintptr_t>(p.y) % 16 == 0);
 #pragma unroll
-      for (int j8 = 0; j8 < CW / 8; ++j8) {
-        const int n = n0 + col0 + j8 * 8;
-        if (n >= p.N) break;
-        __align__(16) OutT o[8];
+        for (int j8 = 0; j8 < CW / 8; ++j8) {
+          const int n = n0 + col0 + j8 * 8;
+          if (n < p.N) {
+            __align__(16) OutT o[8];
 #pragma unroll
-        for (int e = 0; e < 8; ++e) {
-          float r = acc[j8 * 8 + e];
-          if (bias && n + e < p.N) r += Num<OutT>::to_f(bias[n + e]);
-          o[e] = Num<OutT>::from_f(r);
-        }
-        if (vec_ok && n + 8 <= p.N) {
-          *reinterpret_cast<uint4*>(yrow + j8 * 8) = *reinterpret_cast<const uint4*>(o);
-        } else {
-          for (int e = 0; e < 8 && n + e < p.N; ++e) yrow[j8 * 8 + e] = o[e];
+            for (int e = 0; e < 8; ++e) {
+              float r = (e & 1) ? acc[j8 * 4 + e / 2].y : acc[j8 * 4 + e / 2].x;
+              if (bias && n + e < p.N) r += Num<OutT>::to_f(bias[n + e]);
+              o[e] = Num<OutT>::from_f(r);
+            }
+            if (vec_ok && n + 8 <= p.N) {
+              *reinterpret_cast<uint4*>(yrow + j8 * 8) = *reinterpret_cast<const uint4*>(o);
+            } else {
+              for (int e = 0; e < 8 && n + e < p.N; ++e) yrow[j8 * 8 + e] = o[e];
+            }
+          }
         }
       }
     }
   }
 
+teardown:
   tc_fence_before();
   __syncthreads();
   if (warp == 2) {
@@ -293,15 +329,19 @@ int make_map(CUtensorMap* map, const void* ptr, CUtensorMapDataType dt, int esiz
   return MQ_OK;
 }
 
-template <typename OutT, int BN, int CW, int kStages>
+template <typename OutT, int BN, int kStages>
 int launch_gemm(const CUtensorMap& ma, const CUtensorMap& mw, const CUtensorMap& mas, const CUtensorMap& mws,
-                const GemmArgs& p, cudaStream_t st) {
+                GemmArgs p, cudaStream_t st) {
   using L = SmemLayout<BN, kStages>;
-  auto kern = mixed_gemm_kernel<OutT, BN, CW, kStages>;
+  auto kern = mixed_gemm_kernel<OutT, BN, kStages>;
   MQ_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal));
-  dim3 grid((unsigned)((p.N + BN - 1) / BN), (unsigned)((p.M + BM - 1) / BM));
-  dim3 block((kFirstEpiWarp + 4 * BN / CW) * 32);
-  kern<<<grid, block, L::kTotal, st>>>(ma, mw, mas, mws, p);
+  p.debug = mq_get_option("gemm_debug", 0);
+  p.tiles_m = (p.M + BM - 1) / BM;
+  p.tiles_n = (p.N + BN - 1) / BN;
+  const int64_t tiles = (int64_t)p.tiles_m * p.tiles_n;
+  int64_t grid = mq_get_option("gemm_persistent", 0) == 2 ? tiles : (int64_t)mq_sm_count();
+  if (grid > tiles) grid = tiles;
+  kern<<<(unsigned)grid, kThreads, L::kTotal, st>>>(ma, mw, mas, mws, p);
   MQ_CHECK_CUDA(cudaGetLastError());
   return MQ_OK;
 }
@@ -309,8 +349,8 @@ int launch_gemm(const CUtensorMap& ma, const CUtensorMap& mw, const CUtensorMap&
 template <typename OutT>
 int dispatch_gemm(const CUtensorMap& ma, const CUtensorMap& mw, const CUtensorMap& mas, const CUtensorMap& mws,
                   const GemmArgs& p, int bn, cudaStream_t st) {
-  if (bn == 256) return launch_gemm<OutT, 256, 128, 4>(ma, mw, mas, mws, p, st);
-  return launch_gemm<OutT, 128, 64, 6>(ma, mw, mas, mws, p, st);
+  if (bn == 256) return launch_gemm<OutT, 256, 4>(ma, mw, mas, mws, p, st);
+  return launch_gemm<OutT, 128, 6>(ma, mw, mas, mws, p, st);
 }
 
 }  // namespace

@@ -1,0 +1,33 @@
+"""Time the mixed GEMM alone at one shape: python tools/gemm_time.py M N K g p [iters] [debug]"""
+import sys, os, json
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import torch
+from smoothquant_mixedprecision_b200 import ops, _lib
+
+M, N, K, g = (int(v) for v in sys.argv[1:5])
+p = float(sys.argv[5])
+iters = int(sys.argv[6]) if len(sys.argv) > 6 else 10
+debug = int(sys.argv[7]) if len(sys.argv) > 7 else 0
+dev = "cuda"
+torch.manual_seed(0)
+x = (torch.randn(M, K, device=dev) * torch.exp(0.5 * torch.randn(K, device=dev))).half()
+w = (torch.randn(N, K, device=dev) / K ** 0.5).half()
+order = torch.randperm(K, device=dev)
+ks = max(1, int(p * K)) if p > 0 else 0
+perm = order[ks:].int()
+sal = torch.sort(order[:ks]).values.int() if ks else None
+a = ops.quant_rows(x, perm, sal, g)
+wq = ops.quant_rows(w, perm, sal, g)
+_lib.set_option("gemm_debug", debug)
+for _ in range(3):
+    y = ops.mixed_gemm(a, wq, None)
+e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+e0.record()
+for _ in range(iters):
+    y = ops.mixed_gemm(a, wq, None)
+e1.record()
+torch.cuda.synchronize()
+ms = e0.elapsed_time(e1) / iters
+print("GEMM " + json.dumps(dict(M=M, N=N, K=K, g=g, p=p, debug=debug, ms=ms, tops=2.0 * M * N * K / ms / 1e9,
+                                fault=_lib.gemm_fault()[:5])), flush=True)
