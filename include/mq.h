@@ -144,6 +144,12 @@ int mq_set_option(const char* name, int value);
 int mq_quant_fault(unsigned int* out8_host);
 int mq_gemm_fault(unsigned int* out8_host);
 
+/* debug: with option "gemm_profile" != 0 the mixed GEMM records, per CTA, 8 x uint64: kernel cycles, kernel ns,
+ * cycles the TMA producer waited for a free stage, the MMA warp waited for operands / for a free accumulator, the
+ * first epilogue warp waited for an accumulator / for scales, and that warp's busy cycles.  Copies
+ * min(n_ctas, 256) records to out_host (HOST pointer).  Synchronises the device. */
+int mq_gemm_profile(unsigned long long* out_host, int n_ctas);
+
 #ifdef __cplusplus
 }
 #endif

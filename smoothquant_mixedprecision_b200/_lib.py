@@ -37,6 +37,7 @@ SIGNATURES = {
     "mq_set_option": (_i32, [C.c_char_p, _i32]),
     "mq_quant_fault": (_i32, [C.POINTER(C.c_uint)]),
     "mq_gemm_fault": (_i32, [C.POINTER(C.c_uint)]),
+    "mq_gemm_profile": (_i32, [C.POINTER(C.c_ulonglong), _i32]),
 }
 
 
@@ -80,3 +81,10 @@ def quant_fault():
     buf = (C.c_uint * 8)()
     check(lib.mq_quant_fault(buf), "mq_quant_fault")
     return list(buf)
+
+
+def gemm_profile(n_ctas: int = 148):
+    """Per-CTA wait-cycle records of the last mixed GEMM launched with set_option("gemm_profile", 1)."""
+    buf = (C.c_ulonglong * (8 * n_ctas))()
+    check(lib.mq_gemm_profile(buf, n_ctas), "mq_gemm_profile")
+    return [list(buf[i * 8:(i + 1) * 8]) for i in range(n_ctas)]

@@ -49,17 +49,31 @@ struct GemmArgs {
   int kb_int;  // 128-column K blocks of codes holding the G*g quantised columns
   int kb_sal;  // 64-column K blocks of the salient slice
   int tiles_m, tiles_n;
-  int debug;  // bit 0: epilogue skips the rescale math; bit 1: MMA warp issues no MMAs (timing experiments only)
+  int profile;
+  int debug;  // bit 0: epilogue skips the rescale math; bit 1: MMA warp issues no MMAs; bit 2: no TMEM drain (timing only)
 };
+
+constexpr int kScaleSlots = 8;  // ring of per-unit scale vectors (ws[BN] | as[BM], fp32) staged in shared memory by TMA
+
+// optional per-CTA wait-cycle profile (option gemm_profile): 8 x u64 per CTA
+//   [0] kernel cycles  [1] kernel ns  [2] producer waiting for a free smem stage  [3] MMA warp waiting for operands
+//   [4] MMA warp waiting for a free TMEM stage  [5] epilogue warp 4 waiting for an accumulator  [6] .. for scales
+//   [7] epilogue warp 4 busy cycles (drain + rescale + store)
+constexpr int kProfSlots = 8;
+constexpr int kProfCtas = 256;
+__device__ unsigned long long g_gemm_prof[kProfCtas * kProfSlots];
 
 template <int BN, int kStages>
 struct SmemLayout {
   static constexpr int kABytes = BM * kKBlockBytes;
   static constexpr int kBBytes = BN * kKBlockBytes;
   static constexpr int kStageBytes = kABytes + kBBytes;
-  static constexpr int kBarOffset = kStages * kStageBytes;
-  // full[kStages], empty[kStages], tmem_full[2], tmem_empty[2], tmem base (u32)
-  static constexpr int kBarBytes = (2 * kStages + 4) * 8 + 16;
+  // per scale slot: ws[BN] | as[BM]   (fp32)
+  static constexpr int kSlotFloats = BN + BM;
+  static constexpr int kScaleOffset = kStages * kStageBytes;
+  static constexpr int kBarOffset = kScaleOffset + kScaleSlots * kSlotFloats * 4;
+  // full[kStages], empty[kStages], tmem_full[2], tmem_empty[2], sfull[kScaleSlots], sempty[kScaleSlots], tmem base
+  static constexpr int kBarBytes = (2 * kStages + 4 + 2 * kScaleSlots) * 8 + 16;
   static constexpr int kTotal = kBarOffset + kBarBytes + 1024;  // + slack to align the base to 1024 bytes
 };
 
@@ -72,10 +86,20 @@ __device__ __forceinline__ void reg_alloc() {
   asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(kRegs));
 }
 
+// int32 -> fp32 by bit pattern: for |v| < 2^22, bits(kMagic) + v are the bits of the float kMagic + v.  The rescale
+// then needs no subtraction of its own: t = fma(kMagic + v, as, -kMagic * as) is ONE rounding of the exact value
+// v * as, and v * as (<= 13 + 11 bits for fp16-valued scales) is representable, so t == v * as exactly; `as` and
+// -kMagic * as are per-thread scalars of the unit, so the instruction reads one new register.  -kMagic * as =
+// -3 * 2^22 * as is exact whenever `as` has at most 22 significant bits (fp16 / bf16-valued scales have 11 / 8); the
+// two lowest mantissa bits of wider activation scales are cleared so that the identity holds for any input.
+constexpr float kMagic = 12582912.0f;     // 1.5 * 2^23
+constexpr uint32_t kMagicBits = 0x4B400000u;
+
 template <typename OutT, int BN, int kStages>
 __global__ void __launch_bounds__(kThreads, 1)
 mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_w,
                   const __grid_constant__ CUtensorMap map_as, const __grid_constant__ CUtensorMap map_ws,
+                  const __grid_constant__ CUtensorMap map_sa, const __grid_constant__ CUtensorMap map_sw,
                   const GemmArgs p) {
   using L = SmemLayout<BN, kStages>;
   constexpr int CW = BN / 2;  // columns per epilogue thread
@@ -87,13 +111,27 @@ mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
   const uint32_t raw_addr = smem_u32(smem_raw);
   unsigned char* smem = smem_raw + (((raw_addr + 1023u) & ~1023u) - raw_addr);
 
+  float* sscale = reinterpret_cast<float*>(smem + L::kScaleOffset);
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + L::kBarOffset);
   uint64_t* empty_bar = full_bar + kStages;
   uint64_t* tfull_bar = empty_bar + kStages;
   uint64_t* tempty_bar = tfull_bar + 2;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+  uint64_t* sfull_bar = tempty_bar + 2;
+  uint64_t* sempty_bar = sfull_bar + kScaleSlots;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(sempty_bar + kScaleSlots);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const bool prof = p.profile != 0 && blockIdx.x < kProfCtas;
+  const long long k_t0 = clock64();
+  const unsigned long long k_ns0 = globaltimer_ns();
+  long long w0 = 0, w1 = 0;  // wait-cycle accumulators of this thread's role
+  auto timed_wait = [&](uint64_t* bar, uint32_t parity, uint32_t code, long long& accum) -> bool {
+    if (!prof) return mbar_wait(bar, parity, code);
+    const long long t = clock64();  // try_wait may block for a while by itself: time the whole wait
+    const bool ok = mbar_wait(bar, parity, code);
+    accum += clock64() - t;
+    return ok;
+  };
   const int units = p.G + (p.kb_sal > 0 ? 1 : 0);  // accumulation units per tile: K groups, then the salient slice
   const int kb_total = p.kb_int + p.kb_sal;
   const int num_tiles = p.tiles_m * p.tiles_n;
@@ -103,6 +141,8 @@ mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
     tma_prefetch_desc(&map_w);
     tma_prefetch_desc(&map_as);
     tma_prefetch_desc(&map_ws);
+    tma_prefetch_desc(&map_sa);
+    tma_prefetch_desc(&map_sw);
   }
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < kStages; ++s) {
@@ -112,6 +152,10 @@ mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
     for (int t = 0; t < 2; ++t) {
       mbar_init(&tfull_bar[t], 1);
       mbar_init(&tempty_bar[t], kEpiWarps);
+    }
+    for (int s = 0; s < kScaleSlots; ++s) {
+      mbar_init(&sfull_bar[s], 1);
+      mbar_init(&sempty_bar[s], kEpiWarps);
     }
     fence_mbar_init();
   }
@@ -125,12 +169,24 @@ mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
     reg_dealloc<40>();
     if (warp == 0 && lane == 0) {
       // ------------------------------------------------------------------ TMA producer
-      uint32_t kbc = 0;  // K blocks issued so far (ring position)
+      uint32_t kbc = 0, sc = 0;  // K blocks / scale slots issued so far (ring positions)
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
         const int m0 = (tile / p.tiles_n) * BM, n0 = (tile % p.tiles_n) * BN;
+        int u_next = 0;  // next integer unit whose scale vectors have not been requested yet
         for (int kb = 0; kb < kb_total; ++kb, ++kbc) {
+          // scale vectors of every unit that starts inside this K block: ws[u, n0 .. n0+BN) and as[u, m0 .. m0+BM)
+          while (u_next < p.G && u_next * p.g < (kb + 1) * 128) {
+            const uint32_t slot = sc % kScaleSlots;
+            if (!mbar_wait(&sempty_bar[slot], ((sc / kScaleSlots) & 1u) ^ 1u, 0x600u + slot)) goto teardown;
+            float* sl = sscale + slot * L::kSlotFloats;
+            mbar_expect_tx(&sfull_bar[slot], (uint32_t)(L::kSlotFloats * 4));
+            tma_load_2d(sl, &map_sw, n0, u_next, &sfull_bar[slot]);
+            tma_load_2d(sl + BN, &map_sa, m0, u_next, &sfull_bar[slot]);
+            ++u_next;
+            ++sc;
+          }
           const uint32_t s = kbc % kStages, ph = (kbc / kStages) & 1u;
-          if (!mbar_wait(&empty_bar[s], ph ^ 1u, 0x200u + s)) goto teardown;
+          if (!timed_wait(&empty_bar[s], ph ^ 1u, 0x200u + s, w0)) goto teardown;
           unsigned char* sa = smem + (size_t)s * L::kStageBytes;
           unsigned char* sb = sa + L::kABytes;
           mbar_expect_tx(&full_bar[s], (uint32_t)L::kStageBytes);
@@ -154,7 +210,7 @@ mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
         int sub = 0;  // next 32-byte slice inside the current K block (0..3)
         for (int u = 0; u < units; ++u, ++uc) {
           const uint32_t t = uc & 1u;
-          if (!mbar_wait(&tempty_bar[t], ((uc >> 1) & 1u) ^ 1u, 0x300u + t)) goto teardown;
+          if (!timed_wait(&tempty_bar[t], ((uc >> 1) & 1u) ^ 1u, 0x300u + t, w1)) goto teardown;
           tc_fence_after();
           const uint32_t d_tmem = tmem_base + t * BN;
           const bool is_sal = u >= p.G;
@@ -162,7 +218,7 @@ mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
           for (int i = 0; i < n_mma; ++i) {
             const uint32_t s = kbc % kStages;
             if (sub == 0) {
-              if (!mbar_wait(&full_bar[s], (kbc / kStages) & 1u, 0x400u + s)) goto teardown;
+              if (!timed_wait(&full_bar[s], (kbc / kStages) & 1u, 0x400u + s, w0)) goto teardown;
               tc_fence_after();
             }
             const uint32_t sa = smem_u32(smem + (size_t)s * L::kStageBytes);
@@ -194,12 +250,11 @@ mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
     const int ew = warp - kFirstEpiWarp;
     const int quarter = warp & 3;      // TMEM lane quarter this warp may access
     const int col0 = (ew >> 2) * CW;   // first tile column owned by this thread
-    constexpr float kMagic = 12582912.0f;  // 1.5 * 2^23: int32 v (|v| < 2^22) + bits(kMagic) == bits(kMagic + v)
-    const float2 neg_magic = make_float2(-kMagic, -kMagic);
-    uint32_t uc = 0;
+    const int row = quarter * 32 + lane;
+    uint32_t uc = 0, sc = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
       const int m0 = (tile / p.tiles_n) * BM, n0 = (tile % p.tiles_n) * BN;
-      const int m = m0 + quarter * 32 + lane;
+      const int m = m0 + row;
       const bool row_ok = m < p.M;
       float2 acc[CW / 2];
 #pragma unroll
@@ -208,49 +263,67 @@ mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
       for (int u = 0; u < units; ++u, ++uc) {
         const uint32_t t = uc & 1u;
         const bool is_sal = u >= p.G;
-        float as = 1.f;
-        if (!is_sal) as = row_ok ? __ldg(p.a_scales + (int64_t)u * p.ld_as + m) : 0.f;
-        const float2 as2 = make_float2(as, as);
-        const float* wsp = p.w_scales + (int64_t)(is_sal ? 0 : u) * p.ld_ws + n0 + col0;
-        if (!mbar_wait(&tfull_bar[t], (uc >> 1) & 1u, 0x500u + t)) goto teardown;
+        const uint32_t slot = sc % kScaleSlots;
+        const float* sl = sscale + slot * L::kSlotFloats;
+        float2 as2 = make_float2(1.f, 1.f), cas2 = make_float2(0.f, 0.f);
+        if (!is_sal) {
+          if (!timed_wait(&sfull_bar[slot], (sc / kScaleSlots) & 1u, 0x700u + slot, w1)) goto teardown;
+          const float as = __uint_as_float(__float_as_uint(sl[BN + row]) & 0xFFFFFFFCu);
+          as2 = make_float2(as, as);
+          cas2 = make_float2(-kMagic * as, -kMagic * as);
+        }
+        if (!timed_wait(&tfull_bar[t], (uc >> 1) & 1u, 0x500u + t, w0)) goto teardown;
         tc_fence_after();
+        if (p.debug & 4) {  // timing experiment: no TMEM drain at all
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) {
+            mbar_arrive(&tempty_bar[t]);
+            if (!is_sal) mbar_arrive(&sempty_bar[slot]);
+          }
+          if (!is_sal) ++sc;
+          continue;
+        }
         const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + t * BN + (uint32_t)col0;
-        uint32_t v[2][16];
-        tmem_ld_32x16(taddr, v[0]);
+        uint32_t v[2][32];
+        tmem_ld_32x32(taddr, v[0]);
 #pragma unroll
-        for (int c = 0; c < CW / 16; ++c) {
+        for (int c = 0; c < CW / 32; ++c) {
           tmem_ld_wait();
-          if (c + 1 < CW / 16) tmem_ld_32x16(taddr + (uint32_t)((c + 1) * 16), v[(c + 1) & 1]);
-          if (c + 1 == CW / 16) {  // every load of this thread has landed: hand the TMEM stage back to the MMA warp
+          if (c + 1 < CW / 32) tmem_ld_32x32(taddr + (uint32_t)((c + 1) * 32), v[(c + 1) & 1]);
+          if (c + 1 == CW / 32) {  // every load of this thread has landed: hand the TMEM stage back to the MMA warp
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&tempty_bar[t]);
           }
           const uint32_t* vv = v[c & 1];
           if (p.debug & 1) {
-            acc[c * 8].x += __uint_as_float(vv[0]);
+            acc[c * 16].x += __uint_as_float(vv[0]);
           } else if (is_sal) {
 #pragma unroll
-            for (int j = 0; j < 8; ++j)
-              acc[c * 8 + j] = __fadd2_rn(acc[c * 8 + j], make_float2(__uint_as_float(vv[2 * j]),
-                                                                      __uint_as_float(vv[2 * j + 1])));
+            for (int j = 0; j < 16; ++j)
+              acc[c * 16 + j] = __fadd2_rn(acc[c * 16 + j], make_float2(__uint_as_float(vv[2 * j]),
+                                                                        __uint_as_float(vv[2 * j + 1])));
           } else {
+            const float4* ws4 = reinterpret_cast<const float4*>(sl + col0 + c * 32);
 #pragma unroll
-            for (int j4 = 0; j4 < 4; ++j4) {
-              float4 ws = make_float4(0.f, 0.f, 0.f, 0.f);
-              if (n0 + col0 + c * 16 + j4 * 4 < p.N) ws = __ldg(reinterpret_cast<const float4*>(wsp + c * 16 + j4 * 4));
-              float2 f0 = make_float2(__uint_as_float(vv[j4 * 4 + 0] + 0x4B400000u),
-                                      __uint_as_float(vv[j4 * 4 + 1] + 0x4B400000u));
-              float2 f1 = make_float2(__uint_as_float(vv[j4 * 4 + 2] + 0x4B400000u),
-                                      __uint_as_float(vv[j4 * 4 + 3] + 0x4B400000u));
-              f0 = __fadd2_rn(f0, neg_magic);
-              f1 = __fadd2_rn(f1, neg_magic);
-              const float2 s0 = __fmul2_rn(make_float2(ws.x, ws.y), as2);
-              const float2 s1 = __fmul2_rn(make_float2(ws.z, ws.w), as2);
-              acc[c * 8 + j4 * 2 + 0] = __ffma2_rn(f0, s0, acc[c * 8 + j4 * 2 + 0]);
-              acc[c * 8 + j4 * 2 + 1] = __ffma2_rn(f1, s1, acc[c * 8 + j4 * 2 + 1]);
+            for (int q = 0; q < 8; ++q) {
+              const float4 ws = ws4[q];
+              const float2 f0 = make_float2(__uint_as_float(vv[q * 4 + 0] + kMagicBits),
+                                            __uint_as_float(vv[q * 4 + 1] + kMagicBits));
+              const float2 f1 = make_float2(__uint_as_float(vv[q * 4 + 2] + kMagicBits),
+                                            __uint_as_float(vv[q * 4 + 3] + kMagicBits));
+              const float2 t0 = __ffma2_rn(f0, as2, cas2);  // == v * as exactly
+              const float2 t1 = __ffma2_rn(f1, as2, cas2);
+              acc[c * 16 + q * 2 + 0] = __ffma2_rn(t0, make_float2(ws.x, ws.y), acc[c * 16 + q * 2 + 0]);
+              acc[c * 16 + q * 2 + 1] = __ffma2_rn(t1, make_float2(ws.z, ws.w), acc[c * 16 + q * 2 + 1]);
             }
           }
+        }
+        if (!is_sal) {  // scale slot consumed
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&sempty_bar[slot]);
+          ++sc;
         }
       }
 
@@ -281,6 +354,22 @@ mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
   }
 
 teardown:
+  if (prof && lane == 0) {
+    unsigned long long* pr = g_gemm_prof + blockIdx.x * kProfSlots;
+    const long long total = clock64() - k_t0;
+    if (warp == 0) {
+      pr[0] = (unsigned long long)total;
+      pr[1] = globaltimer_ns() - k_ns0;
+      pr[2] = (unsigned long long)w0;
+    } else if (warp == 1) {
+      pr[3] = (unsigned long long)w0;
+      pr[4] = (unsigned long long)w1;
+    } else if (warp == kFirstEpiWarp) {
+      pr[5] = (unsigned long long)w0;
+      pr[6] = (unsigned long long)w1;
+      pr[7] = (unsigned long long)(total - w0 - w1);
+    }
+  }
   tc_fence_before();
   __syncthreads();
   if (warp == 2) {
@@ -309,7 +398,7 @@ EncodeTiledFn get_encode_fn() {
 // 2-D row-major tensor [rows, cols] of `esize`-byte elements with leading dimension ld (elements); box = 128 bytes
 // of the inner dimension x box_rows rows, 128-byte swizzle.
 int make_map(CUtensorMap* map, const void* ptr, CUtensorMapDataType dt, int esize, int64_t rows, int64_t cols,
-             int64_t ld, int box_rows) {
+             int64_t ld, int box_rows, int box_cols = 0) {
   EncodeTiledFn enc = get_encode_fn();
   if (!enc) {
     mq_set_error("cuTensorMapEncodeTiled entry point not available");
@@ -317,10 +406,12 @@ int make_map(CUtensorMap* map, const void* ptr, CUtensorMapDataType dt, int esiz
   }
   cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
   cuuint64_t strides[1] = {(cuuint64_t)ld * (cuuint64_t)esize};
-  cuuint32_t box[2] = {(cuuint32_t)(128 / esize), (cuuint32_t)box_rows};
+  // box_cols == 0: operand tile (128-byte rows, 128-byte swizzle); otherwise a plain row vector of box_cols elements
+  cuuint32_t box[2] = {(cuuint32_t)(box_cols ? box_cols : 128 / esize), (cuuint32_t)box_rows};
   cuuint32_t estr[2] = {1, 1};
   CUresult r = enc(map, dt, 2, const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                   box_cols ? CU_TENSOR_MAP_SWIZZLE_NONE : CU_TENSOR_MAP_SWIZZLE_128B,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     mq_set_error("cuTensorMapEncodeTiled failed with CUresult %d (rows=%lld cols=%lld ld=%lld esize=%d)", (int)r,
                  (long long)rows, (long long)cols, (long long)ld, esize);
@@ -331,26 +422,27 @@ int make_map(CUtensorMap* map, const void* ptr, CUtensorMapDataType dt, int esiz
 
 template <typename OutT, int BN, int kStages>
 int launch_gemm(const CUtensorMap& ma, const CUtensorMap& mw, const CUtensorMap& mas, const CUtensorMap& mws,
-                GemmArgs p, cudaStream_t st) {
+                const CUtensorMap& msa, const CUtensorMap& msw, GemmArgs p, cudaStream_t st) {
   using L = SmemLayout<BN, kStages>;
   auto kern = mixed_gemm_kernel<OutT, BN, kStages>;
   MQ_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal));
   p.debug = mq_get_option("gemm_debug", 0);
+  p.profile = mq_get_option("gemm_profile", 0);
   p.tiles_m = (p.M + BM - 1) / BM;
   p.tiles_n = (p.N + BN - 1) / BN;
   const int64_t tiles = (int64_t)p.tiles_m * p.tiles_n;
   int64_t grid = mq_get_option("gemm_persistent", 0) == 2 ? tiles : (int64_t)mq_sm_count();
   if (grid > tiles) grid = tiles;
-  kern<<<(unsigned)grid, kThreads, L::kTotal, st>>>(ma, mw, mas, mws, p);
+  kern<<<(unsigned)grid, kThreads, L::kTotal, st>>>(ma, mw, mas, mws, msa, msw, p);
   MQ_CHECK_CUDA(cudaGetLastError());
   return MQ_OK;
 }
 
 template <typename OutT>
 int dispatch_gemm(const CUtensorMap& ma, const CUtensorMap& mw, const CUtensorMap& mas, const CUtensorMap& mws,
-                  const GemmArgs& p, int bn, cudaStream_t st) {
-  if (bn == 256) return launch_gemm<OutT, 256, 4>(ma, mw, mas, mws, p, st);
-  return launch_gemm<OutT, 128, 6>(ma, mw, mas, mws, p, st);
+                  const CUtensorMap& msa, const CUtensorMap& msw, const GemmArgs& p, int bn, cudaStream_t st) {
+  if (bn == 256) return launch_gemm<OutT, 256, 4>(ma, mw, mas, mws, msa, msw, p, st);
+  return launch_gemm<OutT, 128, 6>(ma, mw, mas, mws, msa, msw, p, st);
 }
 
 }  // namespace
@@ -387,8 +479,9 @@ int mq_mixed_gemm(const int8_t* a_codes, int64_t lda, const float* a_scales, int
                  (long long)ldw, (long long)kc);
     MQ_CHECK_ARG(reinterpret_cast<uintptr_t>(a_codes) % 16 == 0 && reinterpret_cast<uintptr_t>(w_codes) % 16 == 0,
                  "mq_mixed_gemm: code pointers must be 16-byte aligned");
-    MQ_CHECK_ARG(ld_as >= M && ld_ws >= N && ld_ws % 4 == 0 && reinterpret_cast<uintptr_t>(w_scales) % 16 == 0,
-                 "mq_mixed_gemm: scales need ld_as >= M, ld_ws >= N, ld_ws %% 4 == 0, 16-byte aligned w_scales");
+    MQ_CHECK_ARG(ld_as >= M && ld_ws >= N && ld_ws % 4 == 0 && ld_as % 4 == 0 &&
+                     reinterpret_cast<uintptr_t>(w_scales) % 16 == 0 && reinterpret_cast<uintptr_t>(a_scales) % 16 == 0,
+                 "mq_mixed_gemm: scales need ld_as >= M, ld_ws >= N, ld %% 4 == 0 and 16-byte aligned pointers");
   }
   if (Ks > 0) {
     MQ_CHECK_ARG(a_sal && w_sal && ld_asal >= Ks && ld_wsal >= Ks && ld_asal % 8 == 0 && ld_wsal % 8 == 0,
@@ -399,11 +492,14 @@ int mq_mixed_gemm(const int8_t* a_codes, int64_t lda, const float* a_scales, int
   int bn = mq_get_option("gemm_bn", 0);
   if (bn != 128 && bn != 256) bn = N >= 256 ? 256 : 128;
 
-  CUtensorMap ma, mw, mas, mws;
+  CUtensorMap ma, mw, mas, mws, msa, msw;
   int rc;
   if (G > 0) {
     if ((rc = make_map(&ma, a_codes, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, M, kc, lda, BM))) return rc;
     if ((rc = make_map(&mw, w_codes, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, N, kc, ldw, bn))) return rc;
+    // scale vectors: [G, M] / [G, N] fp32, one row of BM / BN values per unit (rows and columns past M / N read 0)
+    if ((rc = make_map(&msa, a_scales, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, G, M, ld_as, 1, BM))) return rc;
+    if ((rc = make_map(&msw, w_scales, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, G, N, ld_ws, 1, bn))) return rc;
   }
   const CUtensorMapDataType dt16 = dtype == MQ_F16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
   if (Ks > 0) {  // the tensor maps cover exactly Ks columns: TMA zero-fills the tail of the last 64-column block
@@ -416,14 +512,25 @@ int mq_mixed_gemm(const int8_t* a_codes, int64_t lda, const float* a_scales, int
   if (G == 0) {
     ma = mas;
     mw = mws;
+    msa = mas;
+    msw = mws;
   }
   GemmArgs p{};
   p.a_scales = a_scales; p.ld_as = ld_as; p.w_scales = w_scales; p.ld_ws = ld_ws; p.bias = bias;
   p.y = y; p.ldy = ldy; p.M = (int)M; p.N = (int)N; p.G = (int)G; p.g = G > 0 ? group_size : 32;
   p.kb_int = (int)(kc / 128); p.kb_sal = (int)((Ks + 63) / 64);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  if (dtype == MQ_F16) return dispatch_gemm<__half>(ma, mw, mas, mws, p, bn, st);
-  return dispatch_gemm<__nv_bfloat16>(ma, mw, mas, mws, p, bn, st);
+  if (dtype == MQ_F16) return dispatch_gemm<__half>(ma, mw, mas, mws, msa, msw, p, bn, st);
+  return dispatch_gemm<__nv_bfloat16>(ma, mw, mas, mws, msa, msw, p, bn, st);
+}
+
+// debug: per-CTA wait-cycle profile of the last mixed GEMM launched with option gemm_profile != 0 (see kProfSlots).
+// Copies min(n_ctas, 256) x 8 u64 to out_host.  Synchronises the device.
+int mq_gemm_profile(unsigned long long* out_host, int n_ctas) {
+  if (n_ctas > kProfCtas) n_ctas = kProfCtas;
+  if (n_ctas <= 0 || !out_host) return MQ_OK;
+  MQ_CHECK_CUDA(cudaMemcpyFromSymbol(out_host, g_gemm_prof, sizeof(unsigned long long) * kProfSlots * n_ctas));
+  return MQ_OK;
 }
 
 // debug: fault record of the GEMM's bounded waits (see ptx.cuh); clears it.  Synchronises the device.

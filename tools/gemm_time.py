@@ -29,5 +29,16 @@ for _ in range(iters):
 e1.record()
 torch.cuda.synchronize()
 ms = e0.elapsed_time(e1) / iters
+if os.environ.get("MQ_PROFILE"):
+    _lib.set_option("gemm_profile", 1)
+    y = ops.mixed_gemm(a, wq, None)
+    torch.cuda.synchronize()
+    pr = _lib.gemm_profile(148)
+    names = ["cycles", "ns", "prod_wait_empty", "mma_wait_full", "mma_wait_tmem", "epi_wait_acc", "epi_wait_scale", "epi_busy"]
+    import statistics
+    med = {n: statistics.median(r[i] for r in pr) for i, n in enumerate(names)}
+    med["clock_ghz"] = med["cycles"] / max(med["ns"], 1)
+    print("PROF " + json.dumps(med), flush=True)
+    _lib.set_option("gemm_profile", 0)
 print("GEMM " + json.dumps(dict(M=M, N=N, K=K, g=g, p=p, debug=debug, ms=ms, tops=2.0 * M * N * K / ms / 1e9,
                                 fault=_lib.gemm_fault()[:5])), flush=True)
