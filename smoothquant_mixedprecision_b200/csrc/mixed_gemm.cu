@@ -50,7 +50,7 @@ struct GemmArgs {
   int kb_sal;  // 64-column K blocks of the salient slice
   int tiles_m, tiles_n;
   int profile;
-  int debug;  // bit 0: epilogue skips the rescale math; bit 1: MMA warp issues no MMAs; bit 2: no TMEM drain (timing only)
+  int debug;  // bit 1: the MMA warp issues no MMAs (timing experiments only)
 };
 
 constexpr int kScaleSlots = 8;  // ring of per-unit scale vectors (ws[BN] | as[BM], fp32) staged in shared memory by TMA
@@ -95,6 +95,15 @@ __device__ __forceinline__ void reg_alloc() {
 constexpr float kMagic = 12582912.0f;     // 1.5 * 2^23
 constexpr uint32_t kMagicBits = 0x4B400000u;
 
+// bounded wait on the mbarrier at shared address `bar`; returns -1 if it expired, else the cycles it took when
+// profiling (0 otherwise)
+__device__ __forceinline__ long long wait_timed(bool prof, uint32_t bar, uint32_t parity, uint32_t code) {
+  if (!prof) return mbar_wait_a(bar, parity, code) ? 0 : -1;
+  const long long t = clock64();  // try_wait may block for a while by itself: time the whole wait
+  const bool ok = mbar_wait_a(bar, parity, code);
+  return ok ? clock64() - t : -1;
+}
+
 template <typename OutT, int BN, int kStages>
 __global__ void __launch_bounds__(kThreads, 1)
 mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_w,
@@ -124,15 +133,7 @@ mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
   const bool prof = p.profile != 0 && blockIdx.x < kProfCtas;
   const long long k_t0 = clock64();
   const unsigned long long k_ns0 = globaltimer_ns();
-  long long w0 = 0, w1 = 0;  // wait-cycle accumulators of this thread's role
-  auto timed_wait = [&](uint64_t* bar, uint32_t parity, uint32_t code, long long& accum) -> bool {
-    if (!prof) return mbar_wait(bar, parity, code);
-    const long long t = clock64();  // try_wait may block for a while by itself: time the whole wait
-    const bool ok = mbar_wait(bar, parity, code);
-    accum += clock64() - t;
-    return ok;
-  };
-  const int units = p.G + (p.kb_sal > 0 ? 1 : 0);  // accumulation units per tile: K groups, then the salient slice
+  long long w0 = 0, w1 = 0, dt;  // wait-cycle accumulators of this thread's role
   const int kb_total = p.kb_int + p.kb_sal;
   const int num_tiles = p.tiles_m * p.tiles_n;
 
@@ -166,8 +167,11 @@ mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
   const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(tmem_slot);
 
   if (warp < kFirstEpiWarp) {
-    reg_dealloc<40>();
-    if (warp == 0 && lane == 0) {
+    reg_dealloc<88>();
+    // Producer and MMA issuer run as whole warps with warp-uniform control flow; the asynchronous instructions are
+    // issued by one elected lane.  (A `lane == 0` branch around the whole loop makes ptxas treat every operand of
+    // UTMALDG / UTCIMMA as potentially divergent and wrap each issue in a vote / R2UR waterfall.)
+    if (warp == 0) {
       // ------------------------------------------------------------------ TMA producer
       uint32_t kbc = 0, sc = 0;  // K blocks / scale slots issued so far (ring positions)
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
@@ -179,78 +183,102 @@ mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
             const uint32_t slot = sc % kScaleSlots;
             if (!mbar_wait(&sempty_bar[slot], ((sc / kScaleSlots) & 1u) ^ 1u, 0x600u + slot)) goto teardown;
             float* sl = sscale + slot * L::kSlotFloats;
-            mbar_expect_tx(&sfull_bar[slot], (uint32_t)(L::kSlotFloats * 4));
-            tma_load_2d(sl, &map_sw, n0, u_next, &sfull_bar[slot]);
-            tma_load_2d(sl + BN, &map_sa, m0, u_next, &sfull_bar[slot]);
+            if (elect_one()) {
+              mbar_expect_tx(&sfull_bar[slot], (uint32_t)(L::kSlotFloats * 4));
+              tma_load_2d(sl, &map_sw, n0, u_next, &sfull_bar[slot]);
+              tma_load_2d(sl + BN, &map_sa, m0, u_next, &sfull_bar[slot]);
+            }
             ++u_next;
             ++sc;
           }
           const uint32_t s = kbc % kStages, ph = (kbc / kStages) & 1u;
-          if (!timed_wait(&empty_bar[s], ph ^ 1u, 0x200u + s, w0)) goto teardown;
-          unsigned char* sa = smem + (size_t)s * L::kStageBytes;
+          if ((dt = wait_timed(prof, smem_u32(&empty_bar[s]), ph ^ 1u, 0x200u + s)) < 0) goto teardown;
+          w0 += dt;unsigned char* sa = smem + (size_t)s * L::kStageBytes;
           unsigned char* sb = sa + L::kABytes;
-          mbar_expect_tx(&full_bar[s], (uint32_t)L::kStageBytes);
-          if (kb < p.kb_int) {
-            tma_load_2d(sa, &map_a, kb * 128, m0, &full_bar[s]);
-            tma_load_2d(sb, &map_w, kb * 128, n0, &full_bar[s]);
-          } else {
-            const int ks = (kb - p.kb_int) * 64;
-            tma_load_2d(sa, &map_as, ks, m0, &full_bar[s]);
-            tma_load_2d(sb, &map_ws, ks, n0, &full_bar[s]);
+          if (elect_one()) {
+            mbar_expect_tx(&full_bar[s], (uint32_t)L::kStageBytes);
+            if (kb < p.kb_int) {
+              tma_load_2d(sa, &map_a, kb * 128, m0, &full_bar[s]);
+              tma_load_2d(sb, &map_w, kb * 128, n0, &full_bar[s]);
+            } else {
+              const int ks = (kb - p.kb_int) * 64;
+              tma_load_2d(sa, &map_as, ks, m0, &full_bar[s]);
+              tma_load_2d(sb, &map_ws, ks, n0, &full_bar[s]);
+            }
           }
         }
       }
-    } else if (warp == 1 && lane == 0) {
+    } else if (warp == 1) {
       // ------------------------------------------------------------------ MMA issuer
       constexpr uint32_t idesc_i8 = umma_idesc(2u, 1u, BM, BN);
       const uint32_t idesc_f16 = umma_idesc(1u, Num<OutT>::kDtype == MQ_BF16 ? 1u : 0u, BM, BN);
-      const int mma_per_group = p.g / 32;
+      const int slices_per_unit = p.g / 32;  // 32-byte K slices (= MMAs) per integer unit
+      const bool issue = !(p.debug & 2);
       uint32_t kbc = 0, uc = 0;  // K blocks consumed, units issued (ring positions)
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-        int sub = 0;  // next 32-byte slice inside the current K block (0..3)
-        for (int u = 0; u < units; ++u, ++uc) {
+        int u = 0, in_unit = 0;  // integer unit being accumulated, slices already issued into it
+        for (int kb = 0; kb < p.kb_int; ++kb, ++kbc) {
+          const uint32_t s = kbc % kStages;
+          if ((dt = wait_timed(prof, smem_u32(&full_bar[s]), (kbc / kStages) & 1u, 0x400u + s)) < 0) goto teardown;
+          w0 += dt;tc_fence_after();
+          const uint32_t sa = smem_u32(smem + (size_t)s * L::kStageBytes);
+          const uint64_t da = umma_desc_k128(sa), db = umma_desc_k128(sa + L::kABytes);
+#pragma unroll
+          for (int sub = 0; sub < 4; ++sub) {
+            if (u < p.G) {  // slices past the last group are zero padding of the K block
+              const uint32_t t = uc & 1u;
+              if (in_unit == 0) {
+                if ((dt = wait_timed(prof, smem_u32(&tempty_bar[t]), ((uc >> 1) & 1u) ^ 1u, 0x300u + t)) < 0) goto teardown;
+                w1 += dt;tc_fence_after();
+              }
+              if (issue && elect_one())
+                mma_i8_ss(tmem_base + t * BN, da + (uint64_t)(sub * 2), db + (uint64_t)(sub * 2), idesc_i8,
+                          in_unit > 0 ? 1u : 0u);
+              if (++in_unit == slices_per_unit) {
+                if (elect_one()) tc_commit(&tfull_bar[t]);  // accumulator stage t complete -> epilogue
+                in_unit = 0;
+                ++u;
+                ++uc;
+              }
+            }
+          }
+          if (elect_one()) tc_commit(&empty_bar[s]);  // smem stage free once these MMAs have read it
+        }
+        if (p.kb_sal > 0) {  // the salient slice: one more accumulation unit, kind::f16
           const uint32_t t = uc & 1u;
-          if (!timed_wait(&tempty_bar[t], ((uc >> 1) & 1u) ^ 1u, 0x300u + t, w1)) goto teardown;
-          tc_fence_after();
-          const uint32_t d_tmem = tmem_base + t * BN;
-          const bool is_sal = u >= p.G;
-          const int n_mma = is_sal ? p.kb_sal * 4 : mma_per_group;
-          for (int i = 0; i < n_mma; ++i) {
+          if ((dt = wait_timed(prof, smem_u32(&tempty_bar[t]), ((uc >> 1) & 1u) ^ 1u, 0x300u + t)) < 0) goto teardown;
+          w1 += dt;tc_fence_after();
+          for (int kb = 0; kb < p.kb_sal; ++kb, ++kbc) {
             const uint32_t s = kbc % kStages;
-            if (sub == 0) {
-              if (!timed_wait(&full_bar[s], (kbc / kStages) & 1u, 0x400u + s, w0)) goto teardown;
-              tc_fence_after();
-            }
+            if ((dt = wait_timed(prof, smem_u32(&full_bar[s]), (kbc / kStages) & 1u, 0x400u + s)) < 0) goto teardown;
+            w0 += dt;tc_fence_after();
             const uint32_t sa = smem_u32(smem + (size_t)s * L::kStageBytes);
-            const uint64_t da = umma_desc_k128(sa) + (uint64_t)(sub * 2);
-            const uint64_t db = umma_desc_k128(sa + L::kABytes) + (uint64_t)(sub * 2);
-            if (p.debug & 2) {
-            } else if (is_sal)
-              mma_f16_ss(d_tmem, da, db, idesc_f16, i > 0 ? 1u : 0u);
-            else
-              mma_i8_ss(d_tmem, da, db, idesc_i8, i > 0 ? 1u : 0u);
-            if (++sub == 4) {
-              tc_commit(&empty_bar[s]);  // smem stage free once these MMAs have read it
-              ++kbc;
-              sub = 0;
-            }
+            const uint64_t da = umma_desc_k128(sa), db = umma_desc_k128(sa + L::kABytes);
+#pragma unroll
+            for (int sub = 0; sub < 4; ++sub)
+              if (issue && elect_one())
+                mma_f16_ss(tmem_base + t * BN, da + (uint64_t)(sub * 2), db + (uint64_t)(sub * 2), idesc_f16,
+                           (kb | sub) ? 1u : 0u);
+            if (elect_one()) tc_commit(&empty_bar[s]);
           }
-          if (u == p.G - 1 && sub != 0) {  // codes end inside a K block (zero padding): release it
-            tc_commit(&empty_bar[kbc % kStages]);
-            ++kbc;
-            sub = 0;
-          }
-          tc_commit(&tfull_bar[t]);  // accumulator stage t complete -> epilogue
+          if (elect_one()) tc_commit(&tfull_bar[t]);
+          ++uc;
         }
       }
     }
   } else {
     // ------------------------------------------------------------------ epilogue (warps 4..11)
-    reg_alloc<232>();
+    reg_alloc<208>();
     const int ew = warp - kFirstEpiWarp;
     const int quarter = warp & 3;      // TMEM lane quarter this warp may access
     const int col0 = (ew >> 2) * CW;   // first tile column owned by this thread
     const int row = quarter * 32 + lane;
+    // shared-window byte addresses (32-bit) of everything the unit loop touches: no generic-pointer arithmetic inside
+    const uint32_t sscale_a = smem_u32(sscale) + (uint32_t)col0 * 4u;
+    const uint32_t sas_a = smem_u32(sscale) + (uint32_t)(BN + row) * 4u;
+    const uint32_t tfull_a = smem_u32(tfull_bar), tempty_a = smem_u32(tempty_bar);
+    const uint32_t sfull_a = smem_u32(sfull_bar), sempty_a = smem_u32(sempty_bar);
+    const uint32_t tmem_lane = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)col0;
     uint32_t uc = 0, sc = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
       const int m0 = (tile / p.tiles_n) * BM, n0 = (tile % p.tiles_n) * BN;
@@ -260,71 +288,74 @@ mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
 #pragma unroll
       for (int j = 0; j < CW / 2; ++j) acc[j] = make_float2(0.f, 0.f);
 
-      for (int u = 0; u < units; ++u, ++uc) {
-        const uint32_t t = uc & 1u;
-        const bool is_sal = u >= p.G;
-        const uint32_t slot = sc % kScaleSlots;
-        const float* sl = sscale + slot * L::kSlotFloats;
-        float2 as2 = make_float2(1.f, 1.f), cas2 = make_float2(0.f, 0.f);
-        if (!is_sal) {
-          if (!timed_wait(&sfull_bar[slot], (sc / kScaleSlots) & 1u, 0x700u + slot, w1)) goto teardown;
-          const float as = __uint_as_float(__float_as_uint(sl[BN + row]) & 0xFFFFFFFCu);
-          as2 = make_float2(as, as);
-          cas2 = make_float2(-kMagic * as, -kMagic * as);
-        }
-        if (!timed_wait(&tfull_bar[t], (uc >> 1) & 1u, 0x500u + t, w0)) goto teardown;
+      // ---- integer units: acc[n] += (v[n] * as) * ws[n]
+      for (int u = 0; u < p.G; ++u, ++uc, ++sc) {
+        const uint32_t t = uc & 1u, slot = sc % kScaleSlots;
+        const uint32_t slot_off = slot * (uint32_t)(L::kSlotFloats * 4);
+        if ((dt = wait_timed(prof, sfull_a + slot * 8u, (sc / kScaleSlots) & 1u, 0x700u + slot)) < 0) goto teardown;
+        w1 += dt;
+        const float as = __uint_as_float(__float_as_uint(lds_f32(sas_a + slot_off)) & 0xFFFFFFFCu);
+        const float cas = -kMagic * as;
+        if ((dt = wait_timed(prof, tfull_a + t * 8u, (uc >> 1) & 1u, 0x500u + t)) < 0) goto teardown;
+        w0 += dt;
         tc_fence_after();
-        if (p.debug & 4) {  // timing experiment: no TMEM drain at all
-          tc_fence_before();
-          __syncwarp();
-          if (lane == 0) {
-            mbar_arrive(&tempty_bar[t]);
-            if (!is_sal) mbar_arrive(&sempty_bar[slot]);
-          }
-          if (!is_sal) ++sc;
-          continue;
-        }
-        const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + t * BN + (uint32_t)col0;
-        uint32_t v[2][32];
-        tmem_ld_32x32(taddr, v[0]);
+        const uint32_t taddr = tmem_lane + t * BN;
+        const uint32_t ws_a = sscale_a + slot_off;
+        uint32_t v[2][16];
+        tmem_ld_32x16(taddr, v[0]);
 #pragma unroll
-        for (int c = 0; c < CW / 32; ++c) {
+        for (int c = 0; c < CW / 16; ++c) {
           tmem_ld_wait();
-          if (c + 1 < CW / 32) tmem_ld_32x32(taddr + (uint32_t)((c + 1) * 32), v[(c + 1) & 1]);
-          if (c + 1 == CW / 32) {  // every load of this thread has landed: hand the TMEM stage back to the MMA warp
+          if (c + 1 < CW / 16) tmem_ld_32x16(taddr + (uint32_t)((c + 1) * 16), v[(c + 1) & 1]);
+          if (c + 1 == CW / 16) {  // every load of this thread has landed: hand the TMEM stage back to the MMA warp
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(&tempty_bar[t]);
+            if (lane == 0) mbar_arrive_a(tempty_a + t * 8u);
           }
           const uint32_t* vv = v[c & 1];
-          if (p.debug & 1) {
-            acc[c * 16].x += __uint_as_float(vv[0]);
-          } else if (is_sal) {
+          float4 ws[4];
 #pragma unroll
-            for (int j = 0; j < 16; ++j)
-              acc[c * 16 + j] = __fadd2_rn(acc[c * 16 + j], make_float2(__uint_as_float(vv[2 * j]),
-                                                                        __uint_as_float(vv[2 * j + 1])));
-          } else {
-            const float4* ws4 = reinterpret_cast<const float4*>(sl + col0 + c * 32);
+          for (int q = 0; q < 4; ++q) ws[q] = lds_f32x4(ws_a + (uint32_t)((c * 16 + q * 4) * 4));
 #pragma unroll
-            for (int q = 0; q < 8; ++q) {
-              const float4 ws = ws4[q];
-              const float2 f0 = make_float2(__uint_as_float(vv[q * 4 + 0] + kMagicBits),
-                                            __uint_as_float(vv[q * 4 + 1] + kMagicBits));
-              const float2 f1 = make_float2(__uint_as_float(vv[q * 4 + 2] + kMagicBits),
-                                            __uint_as_float(vv[q * 4 + 3] + kMagicBits));
-              const float2 t0 = __ffma2_rn(f0, as2, cas2);  // == v * as exactly
-              const float2 t1 = __ffma2_rn(f1, as2, cas2);
-              acc[c * 16 + q * 2 + 0] = __ffma2_rn(t0, make_float2(ws.x, ws.y), acc[c * 16 + q * 2 + 0]);
-              acc[c * 16 + q * 2 + 1] = __ffma2_rn(t1, make_float2(ws.z, ws.w), acc[c * 16 + q * 2 + 1]);
-            }
+          for (int q = 0; q < 4; ++q) {
+            const int j = q * 4;
+            const float2 f0 = make_float2(__uint_as_float(vv[j + 0] + kMagicBits), __uint_as_float(vv[j + 1] + kMagicBits));
+            const float2 f1 = make_float2(__uint_as_float(vv[j + 2] + kMagicBits), __uint_as_float(vv[j + 3] + kMagicBits));
+            const float2 t0 = __ffma2_rn(f0, make_float2(as, as), make_float2(cas, cas));  // == v * as exactly
+            const float2 t1 = __ffma2_rn(f1, make_float2(as, as), make_float2(cas, cas));
+            acc[c * 8 + q * 2 + 0] = __ffma2_rn(t0, make_float2(ws[q].x, ws[q].y), acc[c * 8 + q * 2 + 0]);
+            acc[c * 8 + q * 2 + 1] = __ffma2_rn(t1, make_float2(ws[q].z, ws[q].w), acc[c * 8 + q * 2 + 1]);
           }
         }
-        if (!is_sal) {  // scale slot consumed
-          __syncwarp();
-          if (lane == 0) mbar_arrive(&sempty_bar[slot]);
-          ++sc;
+        __syncwarp();  // scale slot consumed by every lane
+        if (lane == 0) mbar_arrive_a(sempty_a + slot * 8u);
+      }
+
+      // ---- salient unit (kind::f16, fp32 accumulator): acc[n] += v[n]
+      if (p.kb_sal > 0) {
+        const uint32_t t = uc & 1u;
+        if ((dt = wait_timed(prof, tfull_a + t * 8u, (uc >> 1) & 1u, 0x500u + t)) < 0) goto teardown;
+        w0 += dt;
+        tc_fence_after();
+        const uint32_t taddr = tmem_lane + t * BN;
+        uint32_t v[2][16];
+        tmem_ld_32x16(taddr, v[0]);
+#pragma unroll
+        for (int c = 0; c < CW / 16; ++c) {
+          tmem_ld_wait();
+          if (c + 1 < CW / 16) tmem_ld_32x16(taddr + (uint32_t)((c + 1) * 16), v[(c + 1) & 1]);
+          if (c + 1 == CW / 16) {
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_a(tempty_a + t * 8u);
+          }
+          const uint32_t* vv = v[c & 1];
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            acc[c * 8 + j] = __fadd2_rn(acc[c * 8 + j], make_float2(__uint_as_float(vv[2 * j]),
+                                                                    __uint_as_float(vv[2 * j + 1])));
         }
+        ++uc;
       }
 
       if (row_ok) {  // bias, rounding, store of this thread's row segment (overlaps the next tile's first MMAs)

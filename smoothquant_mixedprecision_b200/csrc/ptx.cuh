@@ -11,6 +11,17 @@ __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));
 }
 
+// one lane of the (fully active) warp; ptxas keeps the operands of the guarded instruction in uniform registers
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "elect.sync _|p, 0xffffffff;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(pred));
+  return pred != 0;
+}
+
 // ------------------------------------------------------------------------------------------------ mbarrier
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
@@ -72,6 +83,56 @@ static __device__ __forceinline__ bool mbar_wait_slow(uint64_t* bar, uint32_t pa
 __device__ __forceinline__ bool mbar_wait(uint64_t* bar, uint32_t parity, uint32_t code) {
   if (mbar_try_wait(bar, parity)) return true;
   return mbar_wait_slow(bar, parity, code);
+}
+
+// Variants on 32-bit shared-window addresses (hot loops: no generic -> shared conversion per use)
+__device__ __forceinline__ void mbar_arrive_a(uint32_t bar_addr) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar_addr) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait_a(uint32_t bar_addr, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(bar_addr), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+static __device__ __forceinline__ bool mbar_wait_slow_a(uint32_t bar_addr, uint32_t parity, uint32_t code) {
+  const unsigned long long t0 = globaltimer_ns();
+  uint32_t spins = 0;
+  while (!mbar_try_wait_a(bar_addr, parity)) {
+    if ((++spins & 0x3FFu) == 0) {
+      const bool aborted = *reinterpret_cast<volatile unsigned int*>(&g_mq_fault[0]) != 0;
+      if (aborted || globaltimer_ns() - t0 > kWaitLimitNs) {
+        if (atomicCAS(&g_mq_fault[0], 0u, code) == 0u) {
+          g_mq_fault[1] = blockIdx.x + (blockIdx.y << 16);
+          g_mq_fault[2] = threadIdx.x;
+          g_mq_fault[3] = parity;
+          g_mq_fault[4] = spins >> 10;
+          __threadfence();
+        }
+        return false;
+      }
+    }
+  }
+  return true;
+}
+__device__ __forceinline__ bool mbar_wait_a(uint32_t bar_addr, uint32_t parity, uint32_t code) {
+  if (mbar_try_wait_a(bar_addr, parity)) return true;
+  return mbar_wait_slow_a(bar_addr, parity, code);
+}
+__device__ __forceinline__ float lds_f32(uint32_t addr) {
+  float r;
+  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(r) : "r"(addr) : "memory");
+  return r;
+}
+__device__ __forceinline__ float4 lds_f32x4(uint32_t addr) {
+  float4 r;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "r"(addr) : "memory");
+  return r;
 }
 
 // ------------------------------------------------------------------------------------------------ fences

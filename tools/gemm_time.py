@@ -34,7 +34,7 @@ if os.environ.get("MQ_PROFILE"):
     y = ops.mixed_gemm(a, wq, None)
     torch.cuda.synchronize()
     pr = _lib.gemm_profile(148)
-    names = ["cycles", "ns", "prod_wait_empty", "mma_wait_full", "mma_wait_tmem", "epi_wait_acc", "epi_wait_scale", "epi_busy"]
+    names = ["cycles", "ns", "epi_wait_ld", "mma_wait_full", "mma_wait_tmem", "epi_wait_acc", "epi_wait_scale", "epi_busy"]
     import statistics
     med = {n: statistics.median(r[i] for r in pr) for i, n in enumerate(names)}
     med["clock_ghz"] = med["cycles"] / max(med["ns"], 1)

@@ -241,6 +241,29 @@ __global__ void __launch_bounds__(256, 1) k_alu2(int iters, long long* cycles, f
           const float2 r0 = __ffma2_rn(t0, make_float2(ws.x, ws.y), make_float2(a[0], a[1]));
           const float2 r1 = __ffma2_rn(t1, make_float2(ws.z, ws.w), make_float2(a[2], a[3]));
           a[0] = r0.x; a[1] = r0.y; a[2] = r1.x; a[3] = r1.y;
+        } else if (form == 4) {  // scalar t (lite/heavy pipes) + packed accumulate (heavy pipe)
+          const float t0 = fmaf(mf[0], as, cas), t1 = fmaf(mf[1], as, cas), t2 = fmaf(mf[2], as, cas),
+                      t3 = fmaf(mf[3], as, cas);
+          const float2 r0 = __ffma2_rn(make_float2(t0, t1), make_float2(ws.x, ws.y), make_float2(a[0], a[1]));
+          const float2 r1 = __ffma2_rn(make_float2(t2, t3), make_float2(ws.z, ws.w), make_float2(a[2], a[3]));
+          a[0] = r0.x; a[1] = r0.y; a[2] = r1.x; a[3] = r1.y;
+        } else if (form == 5) {  // fp32 accumulators (kind::f8f6f4): packed mul + packed fma, no integer op
+          const float2 t0 = __fmul2_rn(make_float2(__uint_as_float(v[q * 4 + 0]), __uint_as_float(v[q * 4 + 1])), as2);
+          const float2 t1 = __fmul2_rn(make_float2(__uint_as_float(v[q * 4 + 2]), __uint_as_float(v[q * 4 + 3])), as2);
+          const float2 r0 = __ffma2_rn(t0, make_float2(ws.x, ws.y), make_float2(a[0], a[1]));
+          const float2 r1 = __ffma2_rn(t1, make_float2(ws.z, ws.w), make_float2(a[2], a[3]));
+          a[0] = r0.x; a[1] = r0.y; a[2] = r1.x; a[3] = r1.y;
+        } else if (form == 6) {  // fp32 accumulators: scalar mul (both fma pipes) + packed fma
+          const float t0 = __uint_as_float(v[q * 4 + 0]) * as, t1 = __uint_as_float(v[q * 4 + 1]) * as,
+                      t2 = __uint_as_float(v[q * 4 + 2]) * as, t3 = __uint_as_float(v[q * 4 + 3]) * as;
+          const float2 r0 = __ffma2_rn(make_float2(t0, t1), make_float2(ws.x, ws.y), make_float2(a[0], a[1]));
+          const float2 r1 = __ffma2_rn(make_float2(t2, t3), make_float2(ws.z, ws.w), make_float2(a[2], a[3]));
+          a[0] = r0.x; a[1] = r0.y; a[2] = r1.x; a[3] = r1.y;
+        } else if (form == 7) {  // fp32 accumulators: all scalar
+          a[0] = fmaf(__uint_as_float(v[q * 4 + 0]) * as, ws.x, a[0]);
+          a[1] = fmaf(__uint_as_float(v[q * 4 + 1]) * as, ws.y, a[1]);
+          a[2] = fmaf(__uint_as_float(v[q * 4 + 2]) * as, ws.z, a[2]);
+          a[3] = fmaf(__uint_as_float(v[q * 4 + 3]) * as, ws.w, a[3]);
         } else {
           a[0] = fmaf((mf[0] - 12582912.0f) * as, ws.x, a[0]);
           a[1] = fmaf((mf[1] - 12582912.0f) * as, ws.y, a[1]);
@@ -420,6 +443,10 @@ int main() {
     k_alu2<1><<<sms, 256>>>(iters, d_cyc, reinterpret_cast<float*>(d_sink), d_ws); rep(1);
     k_alu2<2><<<sms, 256>>>(iters, d_cyc, reinterpret_cast<float*>(d_sink), d_ws); rep(2);
     k_alu2<3><<<sms, 256>>>(iters, d_cyc, reinterpret_cast<float*>(d_sink), d_ws); rep(3);
+    k_alu2<4><<<sms, 256>>>(iters, d_cyc, reinterpret_cast<float*>(d_sink), d_ws); rep(4);
+    k_alu2<5><<<sms, 256>>>(iters, d_cyc, reinterpret_cast<float*>(d_sink), d_ws); rep(5);
+    k_alu2<6><<<sms, 256>>>(iters, d_cyc, reinterpret_cast<float*>(d_sink), d_ws); rep(6);
+    k_alu2<7><<<sms, 256>>>(iters, d_cyc, reinterpret_cast<float*>(d_sink), d_ws); rep(7);
   }
 
   // ---- exact
