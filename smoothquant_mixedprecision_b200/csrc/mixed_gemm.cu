@@ -167,7 +167,7 @@ mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
   const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(tmem_slot);
 
   if (warp < kFirstEpiWarp) {
-    reg_dealloc<88>();
+    reg_dealloc<56>();
     // Producer and MMA issuer run as whole warps with warp-uniform control flow; the asynchronous instructions are
     // issued by one elected lane.  (A `lane == 0` branch around the whole loop makes ptxas treat every operand of
     // UTMALDG / UTCIMMA as potentially divergent and wrap each issue in a vote / R2UR waterfall.)
@@ -268,7 +268,7 @@ mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
     }
   } else {
     // ------------------------------------------------------------------ epilogue (warps 4..11)
-    reg_alloc<208>();
+    reg_alloc<224>();
     const int ew = warp - kFirstEpiWarp;
     const int quarter = warp & 3;      // TMEM lane quarter this warp may access
     const int col0 = (ew >> 2) * CW;   // first tile column owned by this thread
@@ -294,37 +294,41 @@ mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
         const uint32_t slot_off = slot * (uint32_t)(L::kSlotFloats * 4);
         if ((dt = wait_timed(prof, sfull_a + slot * 8u, (sc / kScaleSlots) & 1u, 0x700u + slot)) < 0) goto teardown;
         w1 += dt;
-        const float as = __uint_as_float(__float_as_uint(lds_f32(sas_a + slot_off)) & 0xFFFFFFFCu);
-        const float cas = -kMagic * as;
+        const float as_raw = lds_f32(sas_a + slot_off);  // consumed after the accumulator wait below
         if ((dt = wait_timed(prof, tfull_a + t * 8u, (uc >> 1) & 1u, 0x500u + t)) < 0) goto teardown;
         w0 += dt;
         tc_fence_after();
         const uint32_t taddr = tmem_lane + t * BN;
         const uint32_t ws_a = sscale_a + slot_off;
-        uint32_t v[2][16];
-        tmem_ld_32x16(taddr, v[0]);
+        const float as = __uint_as_float(__float_as_uint(as_raw) & 0xFFFFFFFCu);
+        const float cas = -kMagic * as;
+        uint32_t v[2][32];
+        tmem_ld_32x32(taddr, v[0]);
 #pragma unroll
-        for (int c = 0; c < CW / 16; ++c) {
+        for (int c = 0; c < CW / 32; ++c) {
           tmem_ld_wait();
-          if (c + 1 < CW / 16) tmem_ld_32x16(taddr + (uint32_t)((c + 1) * 16), v[(c + 1) & 1]);
-          if (c + 1 == CW / 16) {  // every load of this thread has landed: hand the TMEM stage back to the MMA warp
+          if (c + 1 < CW / 32) tmem_ld_32x32(taddr + (uint32_t)((c + 1) * 32), v[(c + 1) & 1]);
+          if (c + 1 == CW / 32) {  // every load of this thread has landed: hand the TMEM stage back to the MMA warp
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive_a(tempty_a + t * 8u);
           }
           const uint32_t* vv = v[c & 1];
-          float4 ws[4];
 #pragma unroll
-          for (int q = 0; q < 4; ++q) ws[q] = lds_f32x4(ws_a + (uint32_t)((c * 16 + q * 4) * 4));
+          for (int h = 0; h < 2; ++h) {
+            float4 ws[4];
 #pragma unroll
-          for (int q = 0; q < 4; ++q) {
-            const int j = q * 4;
-            const float2 f0 = make_float2(__uint_as_float(vv[j + 0] + kMagicBits), __uint_as_float(vv[j + 1] + kMagicBits));
-            const float2 f1 = make_float2(__uint_as_float(vv[j + 2] + kMagicBits), __uint_as_float(vv[j + 3] + kMagicBits));
-            const float2 t0 = __ffma2_rn(f0, make_float2(as, as), make_float2(cas, cas));  // == v * as exactly
-            const float2 t1 = __ffma2_rn(f1, make_float2(as, as), make_float2(cas, cas));
-            acc[c * 8 + q * 2 + 0] = __ffma2_rn(t0, make_float2(ws[q].x, ws[q].y), acc[c * 8 + q * 2 + 0]);
-            acc[c * 8 + q * 2 + 1] = __ffma2_rn(t1, make_float2(ws[q].z, ws[q].w), acc[c * 8 + q * 2 + 1]);
+            for (int q = 0; q < 4; ++q) ws[q] = lds_f32x4(ws_a + (uint32_t)((c * 32 + h * 16 + q * 4) * 4));
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              const int j = h * 16 + q * 4;
+              const float2 f0 = make_float2(__uint_as_float(vv[j + 0] + kMagicBits), __uint_as_float(vv[j + 1] + kMagicBits));
+              const float2 f1 = make_float2(__uint_as_float(vv[j + 2] + kMagicBits), __uint_as_float(vv[j + 3] + kMagicBits));
+              const float2 t0 = __ffma2_rn(f0, make_float2(as, as), make_float2(cas, cas));  // == v * as exactly
+              const float2 t1 = __ffma2_rn(f1, make_float2(as, as), make_float2(cas, cas));
+              acc[c * 16 + j / 2 + 0] = __ffma2_rn(t0, make_float2(ws[q].x, ws[q].y), acc[c * 16 + j / 2 + 0]);
+              acc[c * 16 + j / 2 + 1] = __ffma2_rn(t1, make_float2(ws[q].z, ws[q].w), acc[c * 16 + j / 2 + 1]);
+            }
           }
         }
         __syncwarp();  // scale slot consumed by every lane
