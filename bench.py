@@ -33,6 +33,9 @@ SHAPES = {"q_proj": (HIDDEN, HIDDEN), "k_proj": (HIDDEN, HIDDEN), "v_proj": (HID
           "o_proj": (HIDDEN, HIDDEN), "gate_proj": (INTER, HIDDEN), "up_proj": (INTER, HIDDEN),
           "down_proj": (HIDDEN, INTER)}           # name -> (N, K)
 METRIC = "llama2_7b_w4a4_linear_prefill_tokens_per_s"
+# column-parallel plan (smoothquant_mixedprecision_b200/parallel.py: layer_plan_llama)
+PLAN = [("q_proj", False), ("k_proj", False), ("v_proj", True), ("o_proj", True), ("gate_proj", False),
+        ("up_proj", True), ("down_proj", True)]
 
 
 def parse():
@@ -45,6 +48,9 @@ def parse():
     ap.add_argument("--layers", type=int, default=LAYERS)
     ap.add_argument("--cpu-tokens", type=int, default=1024, help="tokens of the bounded CPU sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--parallel", default="dp", choices=["dp", "tp"],
+                    help="N > 1: dp = one replica per GPU over different sequences (weak scaling, no collective); "
+                         "tp = column-parallel over out_features with NCCL all-gathers (strong scaling)")
     return ap.parse_args()
 
 
@@ -155,7 +161,7 @@ class ClockSampler:
                 "samples": len(clocks)}
 
 
-def build_stack(layers, tokens, dev, seed):
+def build_stack(layers, tokens, dev, seed, tp=None):
     """Random-init Llama-2-7B linears packed for mode="fused" (P0 on the GPU) + synthetic calibration statistics."""
     import torch
     from smoothquant_mixedprecision_b200.fake_quant import W4A4Linear
@@ -173,6 +179,8 @@ def build_stack(layers, tokens, dev, seed):
             mods[name] = W4A4Linear.from_float(lin, "per_group", "per_group", importance=imp.cpu(),
                                                salient_prop=SALIENT, group_size=GROUP, mode="fused",
                                                sort_key=imp * 4.0)
+            if tp is not None:        # column-parallel: gather only where the consumer needs the full width
+                mods[name].shard_(tp[0], tp[1], gather_output=dict(PLAN)[name])
             del lin
         stack.append(mods)
     x0 = (torch.randn(tokens, HIDDEN, device=dev, generator=g) * chan[HIDDEN]).half()
@@ -205,7 +213,9 @@ def gpu_arm(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     M = args.tokens
-    stack, x0 = build_stack(args.layers, M, dev, seed=1234 + rank)
+    tp = args.parallel == "tp" and world > 1
+    stack, x0 = build_stack(args.layers, M, dev, seed=1234 + (0 if tp else rank), tp=(rank, world) if tp else None)
+    job_tokens = M if tp else world * M
     hx = torch.empty(x0.shape, dtype=x0.dtype, pin_memory=True).copy_(x0)
     hy = torch.empty(x0.shape, dtype=x0.dtype, pin_memory=True)
     xd = torch.empty_like(x0)
@@ -267,16 +277,18 @@ def gpu_arm(args):
     t_roof_ms = (ops_i8 / (2 * bf16 * 1e12) + ops_f16 / (bf16 * 1e12)) * 1e3
     achieved = (ops_i8 + ops_f16) / (gemm_ms * 1e-3) / 1e12
     peak_mix = (ops_i8 + ops_f16) / (t_roof_ms * 1e-3) / 1e12
-    line = {"metric": METRIC, "value": world * M / (ms * 1e-3), "unit": "tokens/s", "n_gpus": world,
+    line = {"metric": METRIC, "value": job_tokens / (ms * 1e-3), "unit": "tokens/s", "n_gpus": world,
             "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": ms, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "s8 codes (int32 accumulate) + f16 salient",
+            "scaling": "strong" if tp else "weak", "vs_baseline": None,
+            "dtype": "s8 codes (int32 accumulate) + f16 salient",
             "data": "synthetic",
             "config": {"workload": "Llama-2-7B W4A4 linears (224 layers), g=128, 5% salient FP16, static max-sort, "
-                                   "prefill 16x2048 tokens per GPU", "tokens_per_gpu": M, "layers": args.layers,
-                       "group_size": GROUP, "salient_prop": SALIENT, "parallelism": f"dp{world}",
+                                   "prefill 16x2048 tokens per GPU (dp) or per job (tp)", "tokens_per_gpu": M, "layers": args.layers,
+                       "group_size": GROUP, "salient_prop": SALIENT, "parallelism": f"tp{world} (column-parallel, NCCL all-gather of v/o/up/down outputs)" if tp
+                       else f"dp{world}",
                        "l2": "inputs (268 MB activations, 6.9 GB weights) exceed the 126 MB L2; no flush"},
-            "tops": world * M * ops_per_token(args.layers) / (ms * 1e-3) / 1e12,
-            "e2e": {"value": world * M / (ms_e2e * 1e-3), "unit": "tokens/s", "h2d_bytes_per_step": hx.numel() * 2,
+            "tops": job_tokens * ops_per_token(args.layers) / (ms * 1e-3) / 1e12,
+            "e2e": {"value": job_tokens / (ms_e2e * 1e-3), "unit": "tokens/s", "h2d_bytes_per_step": hx.numel() * 2,
                     "d2h_bytes_per_step": hy.numel() * 2, "ms_per_step": ms_e2e},
             "gpu_launches": launches,
             "roofline": {"kernel": "mixed_gemm_kernel", "bound": "tensor", "achieved": achieved, "peak": peak_mix,

@@ -29,7 +29,7 @@ from typing import Dict, Optional
 import torch
 from torch import nn
 
-from . import ops
+from . import ops, parallel
 
 __all__ = [
     "quantize_weight_per_channel_absmax", "quantize_weight_per_tensor_absmax", "quantize_weight_per_group_absmax",
@@ -147,6 +147,8 @@ class W4A4Linear(nn.Module):
         for name in ("w_codes", "w_scales", "w_sal", "perm", "sal_sorted", "keep"):
             self.register_buffer(name, None)
         self.salient_indices = None
+        self.tp_rank, self.tp_world, self.tp_group, self.tp_gather_output = 0, 1, None, True
+        self.full_out_features = out_features
         if importance is not None and salient_prop > 0:
             # fake_quant.py:265-270 -- top max(1, int(p*K)) channels by importance, canonical tie order
             imp = torch.as_tensor(importance).float()
@@ -218,7 +220,38 @@ class W4A4Linear(nn.Module):
             y = self._forward_fused(x2)
         else:
             y = self._forward_reference(x2, act_perm, out_perm)
+        if self.tp_world > 1 and self.tp_gather_output:
+            y = parallel.gather_columns(y, self.full_out_features, self.tp_group)
         return y.view(shape[0], shape[1], -1) if x.dim() == 3 else y
+
+    # ---- column-parallel sharding over out_features; no reference counterpart
+    @torch.no_grad()
+    def shard_(self, rank, world, group=None, gather_output=True):
+        """Keep only the output columns that ``rank`` of ``world`` owns (rows of the packed weight / scales / salient
+        slice / bias).  With ``gather_output`` the forward all-gathers y back to the full width over ``group``;
+        without it the layer returns its [M, N_local] column block (consumer is column-local)."""
+        if self.tp_world != 1:
+            raise RuntimeError("layer is already sharded")
+        if self.output_quant_name != "None":
+            raise ValueError("column-parallel sharding of an output-quantised layer is not supported: the output "
+                             "quantiser groups columns across the whole width (fake_quant.py:309-316)")
+        N = self.out_features
+        lo, hi = parallel.shard_range(N, world, rank)
+        if hi <= lo:
+            raise ValueError(f"rank {rank} of {world} owns no output column of a layer with N={N}")
+        if self.mode == "fused" and self.w_codes is not None:
+            self.w_codes = parallel.shard_rows(self.w_codes, N, world, rank)
+            self.w_sal = parallel.shard_rows(self.w_sal, N, world, rank)
+            self.w_scales = parallel.shard_scales(self.w_scales, N, world, rank)
+        elif self._weight is not None:
+            self._buffers["_weight"] = parallel.shard_rows(self._weight, N, world, rank)
+            object.__setattr__(self, "_w16_cache", None)
+        if self.bias is not None:
+            self._buffers["bias"] = parallel.shard_rows(self.bias.reshape(-1), N, world, rank)
+        self.full_out_features = N
+        self.out_features = hi - lo
+        self.tp_rank, self.tp_world, self.tp_group, self.tp_gather_output = rank, world, group, gather_output
+        return self
 
     def _forward_fused(self, x2):
         cdt = self.w_sal.dtype if self.w_sal is not None else (
@@ -266,7 +299,7 @@ class W4A4Linear(nn.Module):
     @torch.no_grad()
     def from_float(module, weight_quant="per_channel", act_quant="per_token", quantize_output=False, importance=None,
                    salient_prop=0, quant_bits=4, group_size=128, mode="reference", sort="max", sort_key=None,
-                   weight_perm=None):
+                   weight_perm=None, tp_group=None, tp_gather_output=True):
         assert isinstance(module, torch.nn.Linear)                                    # fake_quant.py:335
         _check_choice(weight_quant, _WEIGHT_QUANTS, "weight_quant")                   # ValueError, fake_quant.py:361
         w = module.weight.data
@@ -295,6 +328,9 @@ class W4A4Linear(nn.Module):
                 wq[:, s64] = module.weight.data[:, s64]
             new._buffers["_weight"] = wq
         new._buffers["bias"] = None if module.bias is None else module.bias.data        # shape [N] (:369-370)
+        if tp_group is not None:
+            import torch.distributed as dist
+            new.shard_(dist.get_rank(tp_group), dist.get_world_size(tp_group), tp_group, tp_gather_output)
         return new
 
     def _pack_fused(self, w, key):
@@ -367,7 +403,7 @@ def _swap(parent, attr, prefix, input_feat, guarded, quantize_output, kw, extra)
     setattr(parent, attr, W4A4Linear.from_float(
         getattr(parent, attr), quantize_output=quantize_output, importance=imp,
         sort_key=None if sk is None else sk.get(prefix + "." + attr),
-        mode=extra.get("mode", "reference"), sort=extra.get("sort", "max"), **kw))
+        mode=extra.get("mode", "reference"), sort=extra.get("sort", "max"), tp_group=extra.get("tp_group"), **kw))
 
 
 def quantize_opt(model, weight_quant="per_tensor", act_quant="per_tensor", quantize_bmm_input=True, input_feat=None,

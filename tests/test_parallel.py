@@ -1,0 +1,114 @@
+"""Column-parallel / data-parallel host logic (smoothquant_mixedprecision_b200/parallel.py).
+
+CPU part: world_size-2 gloo processes exercise the shard bookkeeping and the gather / all-reduce plumbing on plain
+tensors (no compute kernels).  GPU part: a fused layer split into column shards on one device reproduces the
+unsharded output bit for bit (the shards run the same kernels on row slices of the packed weight)."""
+import copy
+import os
+import socket
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from smoothquant_mixedprecision_b200 import parallel as P
+
+
+def test_shard_ranges_cover_and_align():
+    for N in (8, 64, 768, 1000, 4096, 11008, 28672):
+        for world in (1, 2, 3, 4, 8):
+            S = P.shard_size(N, world)
+            assert S % 8 == 0 and S * world >= N
+            spans = [P.shard_range(N, world, r) for r in range(world)]
+            assert spans[0][0] == 0 and spans[-1][1] == N
+            for (a, b), (c, d) in zip(spans, spans[1:]):
+                assert b == c and a <= b and c <= d
+    with pytest.raises(ValueError):
+        P.shard_range(64, 2, 2)
+    # 7B shapes at 8 GPUs: 512 and 1376 columns per rank
+    assert P.shard_range(4096, 8, 3) == (1536, 2048) and P.shard_range(11008, 8, 7) == (9632, 11008)
+
+
+def test_split_sequences():
+    for n in (1, 7, 16, 33):
+        for world in (1, 2, 4, 8):
+            spans = [P.split_sequences(n, world, r) for r in range(world)]
+            assert spans[0][0] == 0 and spans[-1][1] == n
+            sizes = [b - a for a, b in spans]
+            assert max(sizes) - min(sizes) <= 1 and all(b == c for (_, b), (c, _) in zip(spans, spans[1:]))
+
+
+def test_shard_scales_layout():
+    sc = torch.arange(3 * 24, dtype=torch.float32).view(3, 24)
+    out = P.shard_scales(sc, 20, 2, 1)             # S = 16 -> rank 1 owns columns 16..19
+    assert out.shape == (3, 4) and torch.equal(out, sc[:, 16:20])
+    out0 = P.shard_scales(sc, 20, 2, 0)
+    assert out0.shape == (3, 16) and torch.equal(out0, sc[:, :16])
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _worker(rank, world, port, N, M):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        g = torch.Generator().manual_seed(7)
+        full = torch.randn(M, N, generator=g).half()
+        lo, hi = P.shard_range(N, world, rank)
+        got = P.gather_columns(full[:, lo:hi].contiguous(), N)
+        assert got.shape == (M, N) and torch.equal(got, full), f"rank {rank}: gather mismatch"
+        out = torch.empty(M, N, dtype=torch.float16)
+        assert P.gather_columns(full[:, lo:hi].contiguous(), N, out=out) is out and torch.equal(out, full)
+        key = torch.full((5,), float(rank))
+        key[rank] = 10.0
+        red = P.allreduce_colmax(key.clone())
+        want = torch.full((5,), float(world - 1))
+        want[:world] = 10.0
+        assert torch.equal(red, want), (rank, red)
+        # per-rank shards of a per-output-channel table reassemble to the table
+        table = torch.arange(N * 3, dtype=torch.float32).view(N, 3)
+        mine = P.shard_rows(table, N, world, rank)
+        parts = [torch.empty(P.shard_size(N, world), 3) for _ in range(world)]
+        pad = torch.zeros(P.shard_size(N, world), 3)
+        pad[: mine.shape[0]] = mine
+        dist.all_gather(parts, pad)
+        assert torch.equal(torch.cat(parts)[:N], table)
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("N,M", [(64, 5), (1000, 3), (11008, 2)])
+def test_gloo_world2_gather_and_allreduce(N, M):
+    mp.spawn(_worker, args=(2, _free_port(), N, M), nprocs=2, join=True)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("world", [2, 8])
+def test_column_shards_reproduce_unsharded_layer(world):
+    from smoothquant_mixedprecision_b200.fake_quant import W4A4Linear
+    torch.manual_seed(3)
+    M, K, N, g = 200, 1024, 1000, 128
+    lin = torch.nn.Linear(K, N).half().cuda()
+    x = (torch.randn(M, K, device="cuda") * torch.exp(0.5 * torch.randn(K, device="cuda"))).half()
+    imp = x.abs().float().mean(dim=0).cpu()
+    for mode in ("fused", "reference"):
+        full = W4A4Linear.from_float(lin, "per_group", "per_group", importance=imp, salient_prop=0.05, group_size=g,
+                                     mode=mode, sort_key=imp)
+        perm = None
+        if mode == "reference":                       # freeze the dynamic permutation so that every shard shares it
+            from smoothquant_mixedprecision_b200 import fake_quant as fq
+            _, keep = full._device_indices(x.device)
+            perm = fq._dynamic_perm(x, subset=keep)
+        y = full(x, act_perm=perm) if mode == "reference" else full(x)
+        parts = []
+        for r in range(world):
+            sh = copy.deepcopy(full).shard_(r, world, gather_output=False)
+            lo, hi = P.shard_range(N, world, r)
+            assert sh.out_features == hi - lo and sh.full_out_features == N
+            parts.append(sh(x, act_perm=perm) if mode == "reference" else sh(x))
+        assert torch.equal(torch.cat(parts, dim=1), y), mode
