@@ -33,9 +33,14 @@ using namespace mqptx;
 
 constexpr int BM = 128;
 constexpr int kKBlockBytes = 128;  // one swizzle atom wide
-constexpr int kFirstEpiWarp = 4;
+// Warp roles.  The epilogue warps come FIRST: the SM sub-partition schedulers favour the highest warp id among the
+// eligible warps, and the two issue warps (TMA producer, MMA issuer) have little to issue but are on the critical
+// path -- with low ids they were starved by the epilogue warps sharing their sub-partition.
 constexpr int kEpiWarps = 8;
-constexpr int kThreads = (kFirstEpiWarp + kEpiWarps) * 32;
+constexpr int kProducerWarp = 8;
+constexpr int kMmaWarp = 9;
+constexpr int kAllocWarp = 10;  // warp 11 idle
+constexpr int kThreads = (kEpiWarps + 4) * 32;
 
 struct GemmArgs {
   const float* a_scales;
@@ -97,14 +102,15 @@ constexpr uint32_t kMagicBits = 0x4B400000u;
 
 // bounded wait on the mbarrier at shared address `bar`; returns -1 if it expired, else the cycles it took when
 // profiling (0 otherwise)
+template <bool kProf>
 __device__ __forceinline__ long long wait_timed(bool prof, uint32_t bar, uint32_t parity, uint32_t code) {
-  if (!prof) return mbar_wait_a(bar, parity, code) ? 0 : -1;
+  if (!kProf || !prof) return mbar_wait_a(bar, parity, code) ? 0 : -1;
   const long long t = clock64();  // try_wait may block for a while by itself: time the whole wait
   const bool ok = mbar_wait_a(bar, parity, code);
   return ok ? clock64() - t : -1;
 }
 
-template <typename OutT, int BN, int kStages>
+template <typename OutT, int BN, int kStages, bool kProf>
 __global__ void __launch_bounds__(kThreads, 1)
 mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_w,
                   const __grid_constant__ CUtensorMap map_as, const __grid_constant__ CUtensorMap map_ws,
@@ -130,14 +136,14 @@ mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(sempty_bar + kScaleSlots);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const bool prof = p.profile != 0 && blockIdx.x < kProfCtas;
-  const long long k_t0 = clock64();
-  const unsigned long long k_ns0 = globaltimer_ns();
+  const bool prof = kProf && p.profile != 0 && blockIdx.x < kProfCtas;
+  const long long k_t0 = kProf ? clock64() : 0;
+  const unsigned long long k_ns0 = kProf ? globaltimer_ns() : 0ull;
   long long w0 = 0, w1 = 0, dt;  // wait-cycle accumulators of this thread's role
   const int kb_total = p.kb_int + p.kb_sal;
   const int num_tiles = p.tiles_m * p.tiles_n;
 
-  if (warp == 0 && lane == 0) {
+  if (warp == kProducerWarp && lane == 0) {
     tma_prefetch_desc(&map_a);
     tma_prefetch_desc(&map_w);
     tma_prefetch_desc(&map_as);
@@ -145,7 +151,7 @@ mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
     tma_prefetch_desc(&map_sa);
     tma_prefetch_desc(&map_sw);
   }
-  if (warp == 1 && lane == 0) {
+  if (warp == kMmaWarp && lane == 0) {
     for (int s = 0; s < kStages; ++s) {
       mbar_init(&full_bar[s], 1);
       mbar_init(&empty_bar[s], 1);
@@ -160,18 +166,18 @@ mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
     }
     fence_mbar_init();
   }
-  if (warp == 2) tmem_alloc<kTmemCols>(tmem_slot);
+  if (warp == kAllocWarp) tmem_alloc<kTmemCols>(tmem_slot);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(tmem_slot);
 
-  if (warp < kFirstEpiWarp) {
-    reg_dealloc<56>();
+  if (warp >= kEpiWarps) {
+    reg_dealloc<40>();
     // Producer and MMA issuer run as whole warps with warp-uniform control flow; the asynchronous instructions are
     // issued by one elected lane.  (A `lane == 0` branch around the whole loop makes ptxas treat every operand of
     // UTMALDG / UTCIMMA as potentially divergent and wrap each issue in a vote / R2UR waterfall.)
-    if (warp == 0) {
+    if (warp == kProducerWarp) {
       // ------------------------------------------------------------------ TMA producer
       uint32_t kbc = 0, sc = 0;  // K blocks / scale slots issued so far (ring positions)
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
@@ -192,8 +198,9 @@ mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
             ++sc;
           }
           const uint32_t s = kbc % kStages, ph = (kbc / kStages) & 1u;
-          if ((dt = wait_timed(prof, smem_u32(&empty_bar[s]), ph ^ 1u, 0x200u + s)) < 0) goto teardown;
-          w0 += dt;unsigned char* sa = smem + (size_t)s * L::kStageBytes;
+          if ((dt = wait_timed<kProf>(prof, smem_u32(&empty_bar[s]), ph ^ 1u, 0x200u + s)) < 0) goto teardown;
+          if (kProf) w0 += dt;
+          unsigned char* sa = smem + (size_t)s * L::kStageBytes;
           unsigned char* sb = sa + L::kABytes;
           if (elect_one()) {
             mbar_expect_tx(&full_bar[s], (uint32_t)L::kStageBytes);
@@ -208,68 +215,98 @@ mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
           }
         }
       }
-    } else if (warp == 1) {
+    } else if (warp == kMmaWarp) {
       // ------------------------------------------------------------------ MMA issuer
+      // Whole warp, warp-uniform control flow, one elected lane issues.  Per K block the elected lane runs ONE asm
+      // block (4 MMAs) plus the commits; descriptors are 32-bit low words advanced by constants.
       constexpr uint32_t idesc_i8 = umma_idesc(2u, 1u, BM, BN);
       const uint32_t idesc_f16 = umma_idesc(1u, Num<OutT>::kDtype == MQ_BF16 ? 1u : 0u, BM, BN);
-      const int slices_per_unit = p.g / 32;  // 32-byte K slices (= MMAs) per integer unit
-      const bool issue = !(p.debug & 2);
+      const bool issue = !(kProf && (p.debug & 2));
+      const uint32_t smem_a = smem_u32(smem);
+      const uint32_t full_a = smem_u32(full_bar), empty_a = smem_u32(empty_bar);
+      const uint32_t tfull_a = smem_u32(tfull_bar), tempty_a = smem_u32(tempty_bar);
+      const int bpu = p.g >= 128 ? p.g / 128 : 1;   // K blocks per unit       (g >= 128)
+      const int upb = p.g >= 128 ? 1 : 128 / p.g;   // units per K block       (g  < 128)
+      const int spu = p.g >= 128 ? 4 : p.g / 32;    // MMAs per unit inside one K block
       uint32_t kbc = 0, uc = 0;  // K blocks consumed, units issued (ring positions)
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-        int u = 0, in_unit = 0;  // integer unit being accumulated, slices already issued into it
-        for (int kb = 0; kb < p.kb_int; ++kb, ++kbc) {
-          const uint32_t s = kbc % kStages;
-          if ((dt = wait_timed(prof, smem_u32(&full_bar[s]), (kbc / kStages) & 1u, 0x400u + s)) < 0) goto teardown;
-          w0 += dt;tc_fence_after();
-          const uint32_t sa = smem_u32(smem + (size_t)s * L::kStageBytes);
-          const uint64_t da = umma_desc_k128(sa), db = umma_desc_k128(sa + L::kABytes);
-#pragma unroll
-          for (int sub = 0; sub < 4; ++sub) {
-            if (u < p.G) {  // slices past the last group are zero padding of the K block
-              const uint32_t t = uc & 1u;
-              if (in_unit == 0) {
-                if ((dt = wait_timed(prof, smem_u32(&tempty_bar[t]), ((uc >> 1) & 1u) ^ 1u, 0x300u + t)) < 0) goto teardown;
-                w1 += dt;tc_fence_after();
+        if (p.g >= 128) {
+          for (int u = 0; u < p.G; ++u, ++uc) {
+            const uint32_t t = uc & 1u;
+            if ((dt = wait_timed<kProf>(prof, tempty_a + t * 8u, ((uc >> 1) & 1u) ^ 1u, 0x300u + t)) < 0) goto teardown;
+            if (kProf) w1 += dt;
+            tc_fence_after();
+            for (int b = 0; b < bpu; ++b, ++kbc) {
+              const uint32_t s = kbc % kStages;
+              if ((dt = wait_timed<kProf>(prof, full_a + s * 8u, (kbc / kStages) & 1u, 0x400u + s)) < 0) goto teardown;
+              if (kProf) w0 += dt;
+              tc_fence_after();
+              const uint32_t sa = smem_a + s * (uint32_t)L::kStageBytes;
+              if (elect_one()) {
+                if (issue)
+                  mma_i8_block4(tmem_base + t * BN, umma_desc_lo(sa), umma_desc_lo(sa + L::kABytes), idesc_i8,
+                                b > 0 ? 1u : 0u);
+                tc_commit_a(empty_a + s * 8u);                    // smem stage free once these MMAs have read it
+                if (b == bpu - 1) tc_commit_a(tfull_a + t * 8u);  // accumulator stage complete -> epilogue
               }
-              if (issue && elect_one())
-                mma_i8_ss(tmem_base + t * BN, da + (uint64_t)(sub * 2), db + (uint64_t)(sub * 2), idesc_i8,
-                          in_unit > 0 ? 1u : 0u);
-              if (++in_unit == slices_per_unit) {
-                if (elect_one()) tc_commit(&tfull_bar[t]);  // accumulator stage t complete -> epilogue
-                in_unit = 0;
-                ++u;
-                ++uc;
-              }
+              __syncwarp();
             }
           }
-          if (elect_one()) tc_commit(&empty_bar[s]);  // smem stage free once these MMAs have read it
+        } else {
+          int u = 0;
+          for (int kb = 0; kb < p.kb_int; ++kb, ++kbc) {
+            const uint32_t s = kbc % kStages;
+            if ((dt = wait_timed<kProf>(prof, full_a + s * 8u, (kbc / kStages) & 1u, 0x400u + s)) < 0) goto teardown;
+            if (kProf) w0 += dt;
+            tc_fence_after();
+            const uint32_t sa = smem_a + s * (uint32_t)L::kStageBytes;
+            const uint32_t la = umma_desc_lo(sa), lb = umma_desc_lo(sa + L::kABytes);
+            for (int h = 0; h < upb && u < p.G; ++h, ++u, ++uc) {  // units past G are zero padding of the K block
+              const uint32_t t = uc & 1u;
+              if ((dt = wait_timed<kProf>(prof, tempty_a + t * 8u, ((uc >> 1) & 1u) ^ 1u, 0x300u + t)) < 0) goto teardown;
+              if (kProf) w1 += dt;
+              tc_fence_after();
+              if (elect_one()) {
+                for (int sub = 0; sub < spu; ++sub) {
+                  const uint32_t off = (uint32_t)((h * spu + sub) * 2);
+                  if (issue) mma_i8_lo(tmem_base + t * BN, la + off, lb + off, idesc_i8, sub > 0 ? 1u : 0u);
+                }
+                tc_commit_a(tfull_a + t * 8u);
+              }
+              __syncwarp();
+            }
+            if (elect_one()) tc_commit_a(empty_a + s * 8u);
+            __syncwarp();
+          }
         }
         if (p.kb_sal > 0) {  // the salient slice: one more accumulation unit, kind::f16
           const uint32_t t = uc & 1u;
-          if ((dt = wait_timed(prof, smem_u32(&tempty_bar[t]), ((uc >> 1) & 1u) ^ 1u, 0x300u + t)) < 0) goto teardown;
-          w1 += dt;tc_fence_after();
+          if ((dt = wait_timed<kProf>(prof, tempty_a + t * 8u, ((uc >> 1) & 1u) ^ 1u, 0x300u + t)) < 0) goto teardown;
+          if (kProf) w1 += dt;
+          tc_fence_after();
           for (int kb = 0; kb < p.kb_sal; ++kb, ++kbc) {
             const uint32_t s = kbc % kStages;
-            if ((dt = wait_timed(prof, smem_u32(&full_bar[s]), (kbc / kStages) & 1u, 0x400u + s)) < 0) goto teardown;
-            w0 += dt;tc_fence_after();
-            const uint32_t sa = smem_u32(smem + (size_t)s * L::kStageBytes);
-            const uint64_t da = umma_desc_k128(sa), db = umma_desc_k128(sa + L::kABytes);
-#pragma unroll
-            for (int sub = 0; sub < 4; ++sub)
-              if (issue && elect_one())
-                mma_f16_ss(tmem_base + t * BN, da + (uint64_t)(sub * 2), db + (uint64_t)(sub * 2), idesc_f16,
-                           (kb | sub) ? 1u : 0u);
-            if (elect_one()) tc_commit(&empty_bar[s]);
+            if ((dt = wait_timed<kProf>(prof, full_a + s * 8u, (kbc / kStages) & 1u, 0x400u + s)) < 0) goto teardown;
+            if (kProf) w0 += dt;
+            tc_fence_after();
+            const uint32_t sa = smem_a + s * (uint32_t)L::kStageBytes;
+            if (elect_one()) {
+              if (issue)
+                mma_f16_block4(tmem_base + t * BN, umma_desc_lo(sa), umma_desc_lo(sa + L::kABytes), idesc_f16,
+                               kb > 0 ? 1u : 0u);
+              tc_commit_a(empty_a + s * 8u);
+              if (kb == p.kb_sal - 1) tc_commit_a(tfull_a + t * 8u);
+            }
+            __syncwarp();
           }
-          if (elect_one()) tc_commit(&tfull_bar[t]);
           ++uc;
         }
       }
     }
   } else {
     // ------------------------------------------------------------------ epilogue (warps 4..11)
-    reg_alloc<224>();
-    const int ew = warp - kFirstEpiWarp;
+    reg_alloc<232>();
+    const int ew = warp;
     const int quarter = warp & 3;      // TMEM lane quarter this warp may access
     const int col0 = (ew >> 2) * CW;   // first tile column owned by this thread
     const int row = quarter * 32 + lane;
@@ -292,43 +329,50 @@ mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
       for (int u = 0; u < p.G; ++u, ++uc, ++sc) {
         const uint32_t t = uc & 1u, slot = sc % kScaleSlots;
         const uint32_t slot_off = slot * (uint32_t)(L::kSlotFloats * 4);
-        if ((dt = wait_timed(prof, sfull_a + slot * 8u, (sc / kScaleSlots) & 1u, 0x700u + slot)) < 0) goto teardown;
-        w1 += dt;
+        if ((dt = wait_timed<kProf>(prof, sfull_a + slot * 8u, (sc / kScaleSlots) & 1u, 0x700u + slot)) < 0) goto teardown;
+        if (kProf) w1 += dt;
         const float as_raw = lds_f32(sas_a + slot_off);  // consumed after the accumulator wait below
-        if ((dt = wait_timed(prof, tfull_a + t * 8u, (uc >> 1) & 1u, 0x500u + t)) < 0) goto teardown;
-        w0 += dt;
+        if ((dt = wait_timed<kProf>(prof, tfull_a + t * 8u, (uc >> 1) & 1u, 0x500u + t)) < 0) goto teardown;
+        if (kProf) w0 += dt;
         tc_fence_after();
         const uint32_t taddr = tmem_lane + t * BN;
         const uint32_t ws_a = sscale_a + slot_off;
         const float as = __uint_as_float(__float_as_uint(as_raw) & 0xFFFFFFFCu);
         const float cas = -kMagic * as;
-        uint32_t v[2][32];
-        tmem_ld_32x32(taddr, v[0]);
+        constexpr int CH = 16;  // columns per TMEM load (double buffered: 2 x CH registers)
+        uint32_t v[2][CH];
+        const bool dbg_nomath = kProf && (p.debug & 4), dbg_noload = kProf && (p.debug & 8);
+        if (!dbg_noload) tmem_ld_32x16(taddr, v[0]);
 #pragma unroll
-        for (int c = 0; c < CW / 32; ++c) {
+        for (int c = 0; c < CW / CH; ++c) {
           tmem_ld_wait();
-          if (c + 1 < CW / 32) tmem_ld_32x32(taddr + (uint32_t)((c + 1) * 32), v[(c + 1) & 1]);
-          if (c + 1 == CW / 32) {  // every load of this thread has landed: hand the TMEM stage back to the MMA warp
+          if (c + 1 < CW / CH && !dbg_noload) tmem_ld_32x16(taddr + (uint32_t)((c + 1) * CH), v[(c + 1) & 1]);
+          if (c + 1 == CW / CH) {  // every load of this thread has landed: hand the TMEM stage back to the MMA warp
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive_a(tempty_a + t * 8u);
           }
           const uint32_t* vv = v[c & 1];
+          if (dbg_nomath) {
+            acc[c].x += __uint_as_float(vv[0]);
+            continue;
+          }
 #pragma unroll
-          for (int h = 0; h < 2; ++h) {
-            float4 ws[4];
-#pragma unroll
-            for (int q = 0; q < 4; ++q) ws[q] = lds_f32x4(ws_a + (uint32_t)((c * 32 + h * 16 + q * 4) * 4));
-#pragma unroll
-            for (int q = 0; q < 4; ++q) {
-              const int j = h * 16 + q * 4;
-              const float2 f0 = make_float2(__uint_as_float(vv[j + 0] + kMagicBits), __uint_as_float(vv[j + 1] + kMagicBits));
-              const float2 f1 = make_float2(__uint_as_float(vv[j + 2] + kMagicBits), __uint_as_float(vv[j + 3] + kMagicBits));
-              const float2 t0 = __ffma2_rn(f0, make_float2(as, as), make_float2(cas, cas));  // == v * as exactly
-              const float2 t1 = __ffma2_rn(f1, make_float2(as, as), make_float2(cas, cas));
-              acc[c * 16 + j / 2 + 0] = __ffma2_rn(t0, make_float2(ws[q].x, ws[q].y), acc[c * 16 + j / 2 + 0]);
-              acc[c * 16 + j / 2 + 1] = __ffma2_rn(t1, make_float2(ws[q].z, ws[q].w), acc[c * 16 + j / 2 + 1]);
-            }
+          for (int q = 0; q < CH / 4; ++q) {
+            const float4 ws = lds_f32x4(ws_a + (uint32_t)((c * CH + q * 4) * 4));
+            const int j = q * 4;
+            const float2 f0 = make_float2(__uint_as_float(vv[j + 0] + kMagicBits), __uint_as_float(vv[j + 1] + kMagicBits));
+            const float2 f1 = make_float2(__uint_as_float(vv[j + 2] + kMagicBits), __uint_as_float(vv[j + 3] + kMagicBits));
+            const float2 t0 = __ffma2_rn(f0, make_float2(as, as), make_float2(cas, cas));  // == v * as exactly
+            const float2 t1 = __ffma2_rn(f1, make_float2(as, as), make_float2(cas, cas));
+            // scalar FMAs here: a packed fma.f32x2 with three distinct 64-bit operands is register-file bound
+            // (5 clk per SMSP, tools/ubench pipe3) while two scalar FMAs take 2.6
+            float2& a0 = acc[(c * CH + j) / 2 + 0];
+            float2& a1 = acc[(c * CH + j) / 2 + 1];
+            a0.x = fmaf(t0.x, ws.x, a0.x);
+            a0.y = fmaf(t0.y, ws.y, a0.y);
+            a1.x = fmaf(t1.x, ws.z, a1.x);
+            a1.y = fmaf(t1.y, ws.w, a1.y);
           }
         }
         __syncwarp();  // scale slot consumed by every lane
@@ -338,8 +382,8 @@ mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
       // ---- salient unit (kind::f16, fp32 accumulator): acc[n] += v[n]
       if (p.kb_sal > 0) {
         const uint32_t t = uc & 1u;
-        if ((dt = wait_timed(prof, tfull_a + t * 8u, (uc >> 1) & 1u, 0x500u + t)) < 0) goto teardown;
-        w0 += dt;
+        if ((dt = wait_timed<kProf>(prof, tfull_a + t * 8u, (uc >> 1) & 1u, 0x500u + t)) < 0) goto teardown;
+        if (kProf) w0 += dt;
         tc_fence_after();
         const uint32_t taddr = tmem_lane + t * BN;
         uint32_t v[2][16];
@@ -389,17 +433,17 @@ mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
   }
 
 teardown:
-  if (prof && lane == 0) {
+  if (kProf && prof && lane == 0) {
     unsigned long long* pr = g_gemm_prof + blockIdx.x * kProfSlots;
     const long long total = clock64() - k_t0;
-    if (warp == 0) {
+    if (warp == kProducerWarp) {
       pr[0] = (unsigned long long)total;
       pr[1] = globaltimer_ns() - k_ns0;
       pr[2] = (unsigned long long)w0;
-    } else if (warp == 1) {
+    } else if (warp == kMmaWarp) {
       pr[3] = (unsigned long long)w0;
       pr[4] = (unsigned long long)w1;
-    } else if (warp == kFirstEpiWarp) {
+    } else if (warp == 0) {
       pr[5] = (unsigned long long)w0;
       pr[6] = (unsigned long long)w1;
       pr[7] = (unsigned long long)(total - w0 - w1);
@@ -407,7 +451,7 @@ teardown:
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 2) {
+  if (warp == kAllocWarp) {
     tc_fence_after();
     tmem_dealloc<kTmemCols>(tmem_base);
   }
@@ -459,10 +503,10 @@ template <typename OutT, int BN, int kStages>
 int launch_gemm(const CUtensorMap& ma, const CUtensorMap& mw, const CUtensorMap& mas, const CUtensorMap& mws,
                 const CUtensorMap& msa, const CUtensorMap& msw, GemmArgs p, cudaStream_t st) {
   using L = SmemLayout<BN, kStages>;
-  auto kern = mixed_gemm_kernel<OutT, BN, kStages>;
-  MQ_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal));
   p.debug = mq_get_option("gemm_debug", 0);
   p.profile = mq_get_option("gemm_profile", 0);
+  auto kern = p.profile ? mixed_gemm_kernel<OutT, BN, kStages, true> : mixed_gemm_kernel<OutT, BN, kStages, false>;
+  MQ_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal));
   p.tiles_m = (p.M + BM - 1) / BM;
   p.tiles_n = (p.N + BN - 1) / BN;
   const int64_t tiles = (int64_t)p.tiles_m * p.tiles_n;

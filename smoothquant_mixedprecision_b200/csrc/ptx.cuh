@@ -61,10 +61,12 @@ __device__ __forceinline__ unsigned long long globaltimer_ns() {
 }
 
 static __device__ __forceinline__ bool mbar_wait_slow(uint64_t* bar, uint32_t parity, uint32_t code) {
-  const unsigned long long t0 = globaltimer_ns();
+  // the global timer is slow to read: it is first sampled after 1024 failed polls, never on the common path
+  unsigned long long t0 = 0;
   uint32_t spins = 0;
   while (!mbar_try_wait(bar, parity)) {
     if ((++spins & 0x3FFu) == 0) {
+      if (spins == 0x400u) t0 = globaltimer_ns();
       const bool aborted = *reinterpret_cast<volatile unsigned int*>(&g_mq_fault[0]) != 0;
       if (aborted || globaltimer_ns() - t0 > kWaitLimitNs) {
         if (atomicCAS(&g_mq_fault[0], 0u, code) == 0u) {
@@ -101,10 +103,12 @@ __device__ __forceinline__ bool mbar_try_wait_a(uint32_t bar_addr, uint32_t pari
   return ok != 0;
 }
 static __device__ __forceinline__ bool mbar_wait_slow_a(uint32_t bar_addr, uint32_t parity, uint32_t code) {
-  const unsigned long long t0 = globaltimer_ns();
+  // the global timer is slow to read: it is first sampled after 1024 failed polls, never on the common path
+  unsigned long long t0 = 0;
   uint32_t spins = 0;
   while (!mbar_try_wait_a(bar_addr, parity)) {
     if ((++spins & 0x3FFu) == 0) {
+      if (spins == 0x400u) t0 = globaltimer_ns();
       const bool aborted = *reinterpret_cast<volatile unsigned int*>(&g_mq_fault[0]) != 0;
       if (aborted || globaltimer_ns() - t0 > kWaitLimitNs) {
         if (atomicCAS(&g_mq_fault[0], 0u, code) == 0u) {
@@ -253,6 +257,49 @@ __device__ __forceinline__ uint64_t umma_desc_k128(uint32_t smem_addr) {
 // [17,23) N >> 3, [24,29) M >> 4.
 __host__ __device__ constexpr uint32_t umma_idesc(uint32_t d_fmt, uint32_t ab_fmt, uint32_t M, uint32_t N) {
   return (d_fmt << 4) | (ab_fmt << 7) | (ab_fmt << 10) | ((N >> 3) << 17) | ((M >> 4) << 24);
+}
+
+// Four consecutive 32-byte K slices of one 128-byte-swizzled K block in ONE asm statement (descriptor low words
+// advance by 32 B >> 4 = 2 per slice; the high word -- SBO 1024 B, version 1, SWIZZLE_128B -- is constant), so that
+// the issuing thread spends a handful of instructions per K block instead of a descriptor rebuild per MMA.
+constexpr uint32_t kDescHiK128 = 0x40004040u;  // == umma_desc_k128(x) >> 32
+#define MQ_MMA_BLOCK4(NAME, KIND)                                                                                   \
+  __device__ __forceinline__ void NAME(uint32_t tmem_d, uint32_t lo_a, uint32_t lo_b, uint32_t idesc,              \
+                                       uint32_t acc_first) {                                                        \
+    asm volatile(                                                                                                   \
+        "{\n\t.reg .pred p, q;\n\t.reg .b64 da, db;\n\t.reg .b32 la, lb;\n\t"                                      \
+        "setp.ne.b32 p, %4, 0;\n\t"                                                                                 \
+        "setp.eq.b32 q, 0, 0;\n\t"                                                                                  \
+        "mov.b64 da, {%1, %5};\n\tmov.b64 db, {%2, %5};\n\t"                                                        \
+        "tcgen05.mma.cta_group::1.kind::" KIND " [%0], da, db, %3, p;\n\t"                                          \
+        "add.u32 la, %1, 2;\n\tadd.u32 lb, %2, 2;\n\tmov.b64 da, {la, %5};\n\tmov.b64 db, {lb, %5};\n\t"            \
+        "tcgen05.mma.cta_group::1.kind::" KIND " [%0], da, db, %3, q;\n\t"                                          \
+        "add.u32 la, %1, 4;\n\tadd.u32 lb, %2, 4;\n\tmov.b64 da, {la, %5};\n\tmov.b64 db, {lb, %5};\n\t"            \
+        "tcgen05.mma.cta_group::1.kind::" KIND " [%0], da, db, %3, q;\n\t"                                          \
+        "add.u32 la, %1, 6;\n\tadd.u32 lb, %2, 6;\n\tmov.b64 da, {la, %5};\n\tmov.b64 db, {lb, %5};\n\t"            \
+        "tcgen05.mma.cta_group::1.kind::" KIND " [%0], da, db, %3, q;\n\t}" ::"r"(tmem_d),                          \
+        "r"(lo_a), "r"(lo_b), "r"(idesc), "r"(acc_first), "r"(kDescHiK128)                                          \
+        : "memory");                                                                                                \
+  }
+MQ_MMA_BLOCK4(mma_i8_block4, "i8")
+MQ_MMA_BLOCK4(mma_f16_block4, "f16")
+#undef MQ_MMA_BLOCK4
+// low word of the K-major SWIZZLE_128B descriptor of the tile at shared address `smem_addr`
+__device__ __forceinline__ uint32_t umma_desc_lo(uint32_t smem_addr) {
+  return ((smem_addr & 0x3FFFFu) >> 4) | (1u << 16);
+}
+__device__ __forceinline__ void mma_i8_lo(uint32_t tmem_d, uint32_t lo_a, uint32_t lo_b, uint32_t idesc,
+                                          uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "mov.b64 da, {%1, %5};\n\tmov.b64 db, {%2, %5};\n\t"
+      "tcgen05.mma.cta_group::1.kind::i8 [%0], da, db, %3, p;\n\t}" ::"r"(tmem_d),
+      "r"(lo_a), "r"(lo_b), "r"(idesc), "r"(accumulate), "r"(kDescHiK128)
+      : "memory");
+}
+__device__ __forceinline__ void tc_commit_a(uint32_t bar_addr) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar_addr) : "memory");
 }
 
 }  // namespace mqptx

@@ -20,6 +20,8 @@ sal = torch.sort(order[:ks]).values.int() if ks else None
 a = ops.quant_rows(x, perm, sal, g)
 wq = ops.quant_rows(w, perm, sal, g)
 _lib.set_option("gemm_debug", debug)
+if debug:
+    _lib.set_option("gemm_profile", 1)      # the debug bits live in the profiling variant of the kernel
 for _ in range(3):
     y = ops.mixed_gemm(a, wq, None)
 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)

@@ -287,6 +287,84 @@ __global__ void __launch_bounds__(256, 1) k_alu2(int iters, long long* cycles, f
   }
 }
 
+
+// ------------------------------------------------------------------------------------------------ pipe
+// Issue / pipe throughput of the epilogue's instruction kinds, 8 warps (2 per SMSP), 16 independent chains per thread.
+//  mix 0: FFMA2 only   1: FFMA only   2: FFMA2 + 2 FFMA (same lane-ops on packed and scalar)   3: FFMA2 + VIADD
+//  mix 4: FFMA + VIADD   5: FFMA2 + FFMA + VIADD   6: FFMA2 + FFMA
+template <int mix>
+__global__ void __launch_bounds__(256, 1) k_pipe(int iters, long long* cycles, float* sink, float a, float b) {
+  float2 acc2[16];
+  float acc[32];
+  uint32_t iv[16];
+#pragma unroll
+  for (int j = 0; j < 16; ++j) { acc2[j] = make_float2(threadIdx.x + j, j); iv[j] = threadIdx.x * 3 + j; }
+#pragma unroll
+  for (int j = 0; j < 32; ++j) acc[j] = threadIdx.x - j;
+  const float2 a2 = make_float2(a, a), b2 = make_float2(b, b);
+  const long long t0 = clock64();
+  for (int it = 0; it < iters; ++it) {
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+      if (mix == 0 || mix == 2 || mix == 3 || mix == 5 || mix == 6) acc2[j] = __ffma2_rn(acc2[j], a2, b2);
+      if (mix == 1 || mix == 4 || mix == 5 || mix == 6) acc[j] = fmaf(acc[j], a, b);
+      if (mix == 2) { acc[2 * j] = fmaf(acc[2 * j], a, b); acc[2 * j + 1] = fmaf(acc[2 * j + 1], a, b); }
+      if (mix == 3 || mix == 4 || mix == 5) iv[j] = iv[j] + 0x4B400000u;
+    }
+  }
+  const long long t1 = clock64();
+  if (threadIdx.x == 0) cycles[blockIdx.x] = t1 - t0;
+  float sum = 0.f;
+#pragma unroll
+  for (int j = 0; j < 16; ++j) sum += acc2[j].x + acc2[j].y + __uint_as_float(iv[j]);
+#pragma unroll
+  for (int j = 0; j < 32; ++j) sum += acc[j];
+  if (sum == 1.2345f) sink[0] = sum;
+}
+
+
+// pipe3: FMAs whose three operands are all distinct registers (like acc = fma(t, ws, acc) in the epilogue)
+//  mix 0: 16 FFMA2 (3 distinct 64-bit operands)   1: 32 FFMA (3 distinct 32-bit operands)   2: 16 FFMA2 with scalar a, b
+//  mix 3: 8 FFMA2 3-op + 8 FFMA2 scalar-broadcast form (the epilogue's pair per 2 elements), + 16 VIADD
+template <int mix>
+__global__ void __launch_bounds__(256, 1) k_pipe3(int iters, long long* cycles, float* sink, float a, float b) {
+  float2 acc2[16], x2[16], y2[16];
+  uint32_t iv[16];
+#pragma unroll
+  for (int j = 0; j < 16; ++j) {
+    acc2[j] = make_float2(threadIdx.x + j, j);
+    x2[j] = make_float2(1.0f + 1e-6f * (threadIdx.x + j), 1.0f - 1e-6f * j);
+    y2[j] = make_float2(a * j, b * (threadIdx.x & 3));
+    iv[j] = threadIdx.x + j;
+  }
+  const long long t0 = clock64();
+  for (int it = 0; it < iters; ++it) {
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+      if (mix == 0) acc2[j] = __ffma2_rn(x2[j], y2[(j + 5) & 15], acc2[j]);
+      if (mix == 1) {
+        acc2[j].x = fmaf(x2[j].x, y2[(j + 5) & 15].x, acc2[j].x);
+        acc2[j].y = fmaf(x2[j].y, y2[(j + 5) & 15].y, acc2[j].y);
+      }
+      if (mix == 2) acc2[j] = __ffma2_rn(acc2[j], make_float2(a, a), make_float2(b, b));
+      if (mix == 3) {
+        if (j & 1) {
+          acc2[j] = __ffma2_rn(x2[j], y2[(j + 5) & 15], acc2[j]);
+        } else {
+          x2[j + 1] = __ffma2_rn(make_float2(__uint_as_float(iv[j]), __uint_as_float(iv[j + 1])), make_float2(a, a), make_float2(b, b));
+        }
+        iv[j] = iv[j] + 0x4B400000u;
+      }
+    }
+  }
+  const long long t1 = clock64();
+  if (threadIdx.x == 0) cycles[blockIdx.x] = t1 - t0;
+  float sum = 0.f;
+#pragma unroll
+  for (int j = 0; j < 16; ++j) sum += acc2[j].x + acc2[j].y + x2[j].x + y2[j].y + __uint_as_float(iv[j]);
+  if (sum == 1.2345f) sink[0] = sum;
+}
+
 // ------------------------------------------------------------------------------------------------ exact
 // One CTA: A (128 rows) and B (256 rows) tiles of nblk 128-byte K blocks with int8 codes in [-7, 7] (any layout:
 // both kinds read the same bytes through the same descriptors).  i8 result -> out_i, f8 (bytes translated to E4M3)
@@ -403,6 +481,40 @@ int main() {
       printf("UB mma kind=%s fill=%d clk/mma=%.1f ms=%.3f eff_clock_GHz=%.3f chip_Tops=%.1f\n", kn[kind], fill, cyc, ms,
              med(h) / (ms * 1e6), 2.0 * macs / (ms * 1e-3) / 1e12);
     }
+
+
+  // ---- pipe
+  {
+    const int iters = 2000;
+    auto rep = [&](int mix, const char* what) {
+      CK(cudaDeviceSynchronize());
+      CK(cudaMemcpy(h.data(), d_cyc, sms * sizeof(long long), cudaMemcpyDeviceToHost));
+      printf("UB pipe mix=%d (%s) clk per 16-chain step (2 warps/SMSP)=%.2f\n", mix, what, med(h) / iters);
+    };
+    float* fs = reinterpret_cast<float*>(d_sink);
+    k_pipe<0><<<sms, 256>>>(iters, d_cyc, fs, 1.0001f, 0.5f); rep(0, "16 FFMA2");
+    k_pipe<1><<<sms, 256>>>(iters, d_cyc, fs, 1.0001f, 0.5f); rep(1, "16 FFMA");
+    k_pipe<2><<<sms, 256>>>(iters, d_cyc, fs, 1.0001f, 0.5f); rep(2, "16 FFMA2 + 32 FFMA");
+    k_pipe<3><<<sms, 256>>>(iters, d_cyc, fs, 1.0001f, 0.5f); rep(3, "16 FFMA2 + 16 VIADD");
+    k_pipe<4><<<sms, 256>>>(iters, d_cyc, fs, 1.0001f, 0.5f); rep(4, "16 FFMA + 16 VIADD");
+    k_pipe<5><<<sms, 256>>>(iters, d_cyc, fs, 1.0001f, 0.5f); rep(5, "16 FFMA2 + 16 FFMA + 16 VIADD");
+    k_pipe<6><<<sms, 256>>>(iters, d_cyc, fs, 1.0001f, 0.5f); rep(6, "16 FFMA2 + 16 FFMA");
+  }
+
+
+  {
+    const int iters = 2000;
+    auto rep = [&](int mix, const char* what) {
+      CK(cudaDeviceSynchronize());
+      CK(cudaMemcpy(h.data(), d_cyc, sms * sizeof(long long), cudaMemcpyDeviceToHost));
+      printf("UB pipe3 mix=%d (%s) clk per step (2 warps/SMSP)=%.2f\n", mix, what, med(h) / iters);
+    };
+    float* fs = reinterpret_cast<float*>(d_sink);
+    k_pipe3<0><<<sms, 256>>>(iters, d_cyc, fs, 1.0001f, 0.5f); rep(0, "16 FFMA2 3 distinct operands");
+    k_pipe3<1><<<sms, 256>>>(iters, d_cyc, fs, 1.0001f, 0.5f); rep(1, "32 FFMA 3 distinct operands");
+    k_pipe3<2><<<sms, 256>>>(iters, d_cyc, fs, 1.0001f, 0.5f); rep(2, "16 FFMA2 scalar a,b");
+    k_pipe3<3><<<sms, 256>>>(iters, d_cyc, fs, 1.0001f, 0.5f); rep(3, "8 FFMA2 3-op + 8 FFMA2 scalar + 16 VIADD");
+  }
 
   // ---- ldtm
   {
