@@ -40,13 +40,16 @@ def _stale(target: str, deps) -> bool:
 
 def build(force: bool = False, verbose: bool = False) -> str:
     nvcc = _nvcc()
+    extra = os.environ.get("MQ_NVCC_EXTRA", "").split()      # experiments only (e.g. -DMQ_GEMM_PRELOAD=0)
+    if extra:
+        force = True
     os.makedirs(BUILD, exist_ok=True)
     jobs = []
     for src in SOURCES:
         s = os.path.join(CSRC, src)
         o = os.path.join(BUILD, src.replace(".cu", ".o"))
         if force or _stale(o, [s] + HEADERS):
-            jobs.append([nvcc, *NVCC_FLAGS, "-c", s, "-o", o])
+            jobs.append([nvcc, *NVCC_FLAGS, *extra, "-c", s, "-o", o])
 
     def run(cmd):
         if verbose:

@@ -58,6 +58,13 @@ struct GemmArgs {
   int debug;  // bit 1: the MMA warp issues no MMAs (timing experiments only)
 };
 
+// kPreload: the epilogue refills every drained TMEM accumulator stage with the bit pattern of 1.5 * 2^23 and the
+// integer MMAs always accumulate, so that the drained int32 words ARE the floats kMagic + sum: the per-element
+// integer add of the magic-number conversion disappears from the epilogue (1/3 of its instructions).
+#ifndef MQ_GEMM_PRELOAD
+#define MQ_GEMM_PRELOAD 1
+#endif
+constexpr bool kPreload = MQ_GEMM_PRELOAD != 0;
 constexpr int kScaleSlots = 8;  // ring of per-unit scale vectors (ws[BN] | as[BM], fp32) staged in shared memory by TMA
 
 // optional per-CTA wait-cycle profile (option gemm_profile): 8 x u64 per CTA
@@ -221,7 +228,14 @@ mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
       // block (4 MMAs) plus the commits; descriptors are 32-bit low words advanced by constants.
       constexpr uint32_t idesc_i8 = umma_idesc(2u, 1u, BM, BN);
       const uint32_t idesc_f16 = umma_idesc(1u, Num<OutT>::kDtype == MQ_BF16 ? 1u : 0u, BM, BN);
+#ifdef MQ_DEBUG_NOMMA
+      const bool issue = false;
+#else
       const bool issue = !(kProf && (p.debug & 2));
+#endif
+      // without preload the first use of a TMEM stage finds it free (wait on the inverted parity); with preload the
+      // epilogue's initial fill is completion #0 of the stage's empty barrier
+      constexpr uint32_t kEmptyFlip = kPreload ? 0u : 1u;
       const uint32_t smem_a = smem_u32(smem);
       const uint32_t full_a = smem_u32(full_bar), empty_a = smem_u32(empty_bar);
       const uint32_t tfull_a = smem_u32(tfull_bar), tempty_a = smem_u32(tempty_bar);
@@ -233,7 +247,7 @@ mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
         if (p.g >= 128) {
           for (int u = 0; u < p.G; ++u, ++uc) {
             const uint32_t t = uc & 1u;
-            if ((dt = wait_timed<kProf>(prof, tempty_a + t * 8u, ((uc >> 1) & 1u) ^ 1u, 0x300u + t)) < 0) goto teardown;
+            if ((dt = wait_timed<kProf>(prof, tempty_a + t * 8u, ((uc >> 1) & 1u) ^ kEmptyFlip, 0x300u + t)) < 0) goto teardown;
             if (kProf) w1 += dt;
             tc_fence_after();
             for (int b = 0; b < bpu; ++b, ++kbc) {
@@ -245,7 +259,7 @@ mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
               if (elect_one()) {
                 if (issue)
                   mma_i8_block4(tmem_base + t * BN, umma_desc_lo(sa), umma_desc_lo(sa + L::kABytes), idesc_i8,
-                                b > 0 ? 1u : 0u);
+                                (kPreload || b > 0) ? 1u : 0u);
                 tc_commit_a(empty_a + s * 8u);                    // smem stage free once these MMAs have read it
                 if (b == bpu - 1) tc_commit_a(tfull_a + t * 8u);  // accumulator stage complete -> epilogue
               }
@@ -263,13 +277,13 @@ mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
             const uint32_t la = umma_desc_lo(sa), lb = umma_desc_lo(sa + L::kABytes);
             for (int h = 0; h < upb && u < p.G; ++h, ++u, ++uc) {  // units past G are zero padding of the K block
               const uint32_t t = uc & 1u;
-              if ((dt = wait_timed<kProf>(prof, tempty_a + t * 8u, ((uc >> 1) & 1u) ^ 1u, 0x300u + t)) < 0) goto teardown;
+              if ((dt = wait_timed<kProf>(prof, tempty_a + t * 8u, ((uc >> 1) & 1u) ^ kEmptyFlip, 0x300u + t)) < 0) goto teardown;
               if (kProf) w1 += dt;
               tc_fence_after();
               if (elect_one()) {
                 for (int sub = 0; sub < spu; ++sub) {
                   const uint32_t off = (uint32_t)((h * spu + sub) * 2);
-                  if (issue) mma_i8_lo(tmem_base + t * BN, la + off, lb + off, idesc_i8, sub > 0 ? 1u : 0u);
+                  if (issue) mma_i8_lo(tmem_base + t * BN, la + off, lb + off, idesc_i8, (kPreload || sub > 0) ? 1u : 0u);
                 }
                 tc_commit_a(tfull_a + t * 8u);
               }
@@ -281,7 +295,7 @@ mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
         }
         if (p.kb_sal > 0) {  // the salient slice: one more accumulation unit, kind::f16
           const uint32_t t = uc & 1u;
-          if ((dt = wait_timed<kProf>(prof, tempty_a + t * 8u, ((uc >> 1) & 1u) ^ 1u, 0x300u + t)) < 0) goto teardown;
+          if ((dt = wait_timed<kProf>(prof, tempty_a + t * 8u, ((uc >> 1) & 1u) ^ kEmptyFlip, 0x300u + t)) < 0) goto teardown;
           if (kProf) w1 += dt;
           tc_fence_after();
           for (int kb = 0; kb < p.kb_sal; ++kb, ++kbc) {
@@ -317,6 +331,21 @@ mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
     const uint32_t sfull_a = smem_u32(sfull_bar), sempty_a = smem_u32(sempty_bar);
     const uint32_t tmem_lane = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)col0;
     uint32_t uc = 0, sc = 0;
+    uint32_t magic[8];
+    if (kPreload) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) asm volatile("mov.u32 %0, 0x4B400000;" : "=r"(magic[i]));  // opaque: stays in registers
+#pragma unroll 1
+      for (int c = 0; c < 2 * BN / 8; ++c)
+        if ((c * 8) % BN >= col0 && (c * 8) % BN < col0 + CW) tmem_st_32x8(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(c * 8), magic);
+      tmem_st_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) {
+        mbar_arrive_a(tempty_a);
+        mbar_arrive_a(tempty_a + 8u);
+      }
+    }
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
       const int m0 = (tile / p.tiles_n) * BM, n0 = (tile % p.tiles_n) * BN;
       const int m = m0 + row;
@@ -341,28 +370,46 @@ mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
         const float cas = -kMagic * as;
         constexpr int CH = 16;  // columns per TMEM load (double buffered: 2 x CH registers)
         uint32_t v[2][CH];
+#ifdef MQ_DEBUG_NOLDTM
+        const bool dbg_nomath = kProf && (p.debug & 4), dbg_noload = true;
+#else
         const bool dbg_nomath = kProf && (p.debug & 4), dbg_noload = kProf && (p.debug & 8);
+#endif
         if (!dbg_noload) tmem_ld_32x16(taddr, v[0]);
 #pragma unroll
         for (int c = 0; c < CW / CH; ++c) {
           tmem_ld_wait();
           if (c + 1 < CW / CH && !dbg_noload) tmem_ld_32x16(taddr + (uint32_t)((c + 1) * CH), v[(c + 1) & 1]);
+          if (kPreload) {  // chunk c has been read: refill it
+            tmem_st_32x8(taddr + (uint32_t)(c * CH), magic);
+            tmem_st_32x8(taddr + (uint32_t)(c * CH + 8), magic);
+          }
           if (c + 1 == CW / CH) {  // every load of this thread has landed: hand the TMEM stage back to the MMA warp
+            if (kPreload) tmem_st_wait();
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive_a(tempty_a + t * 8u);
           }
           const uint32_t* vv = v[c & 1];
+#ifdef MQ_DEBUG_NOMATH
+          acc[c].x += __uint_as_float(vv[0]) + __uint_as_float(vv[15]);
+          continue;
+#endif
           if (dbg_nomath) {
             acc[c].x += __uint_as_float(vv[0]);
             continue;
           }
 #pragma unroll
           for (int q = 0; q < CH / 4; ++q) {
+#ifdef MQ_DEBUG_NOLDS   // timing experiment only: no shared-memory read of the weight scales (wrong results)
+            const float4 ws = make_float4(as_raw, cas, as_raw, cas);
+#else
             const float4 ws = lds_f32x4(ws_a + (uint32_t)((c * CH + q * 4) * 4));
+#endif
             const int j = q * 4;
-            const float2 f0 = make_float2(__uint_as_float(vv[j + 0] + kMagicBits), __uint_as_float(vv[j + 1] + kMagicBits));
-            const float2 f1 = make_float2(__uint_as_float(vv[j + 2] + kMagicBits), __uint_as_float(vv[j + 3] + kMagicBits));
+            constexpr uint32_t kAdd = kPreload ? 0u : kMagicBits;
+            const float2 f0 = make_float2(__uint_as_float(vv[j + 0] + kAdd), __uint_as_float(vv[j + 1] + kAdd));
+            const float2 f1 = make_float2(__uint_as_float(vv[j + 2] + kAdd), __uint_as_float(vv[j + 3] + kAdd));
             const float2 t0 = __ffma2_rn(f0, make_float2(as, as), make_float2(cas, cas));  // == v * as exactly
             const float2 t1 = __ffma2_rn(f1, make_float2(as, as), make_float2(cas, cas));
             // scalar FMAs here: a packed fma.f32x2 with three distinct 64-bit operands is register-file bound
@@ -392,7 +439,12 @@ mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
         for (int c = 0; c < CW / 16; ++c) {
           tmem_ld_wait();
           if (c + 1 < CW / 16) tmem_ld_32x16(taddr + (uint32_t)((c + 1) * 16), v[(c + 1) & 1]);
+          if (kPreload && p.G > 0) {
+            tmem_st_32x8(taddr + (uint32_t)(c * 16), magic);
+            tmem_st_32x8(taddr + (uint32_t)(c * 16 + 8), magic);
+          }
           if (c + 1 == CW / 16) {
+            if (kPreload) tmem_st_wait();
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive_a(tempty_a + t * 8u);

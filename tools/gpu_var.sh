@@ -1,0 +1,8 @@
+#!/bin/bash
+# time prebuilt experimental variants of libmq.so (tools/libmq_*.so); results are not checked
+cp smoothquant_mixedprecision_b200/libmq.so /tmp/libmq_orig.so
+for f in tools/libmq_*.so; do
+  cp $f smoothquant_mixedprecision_b200/libmq.so
+  echo "== $f"; python tools/gemm_time.py 32768 4096 4096 128 0.05 10 0 2>&1 | grep GEMM | cut -c1-150
+done
+cp /tmp/libmq_orig.so smoothquant_mixedprecision_b200/libmq.so
