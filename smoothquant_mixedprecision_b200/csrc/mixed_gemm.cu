@@ -36,11 +36,19 @@ constexpr int kKBlockBytes = 128;  // one swizzle atom wide
 // Warp roles.  The epilogue warps come FIRST: the SM sub-partition schedulers favour the highest warp id among the
 // eligible warps, and the two issue warps (TMA producer, MMA issuer) have little to issue but are on the critical
 // path -- with low ids they were starved by the epilogue warps sharing their sub-partition.
-constexpr int kEpiWarps = 8;
-constexpr int kProducerWarp = 8;
-constexpr int kMmaWarp = 9;
-constexpr int kAllocWarp = 10;  // warp 11 idle
+#ifndef MQ_GEMM_EPI_WARPS
+#define MQ_GEMM_EPI_WARPS 8
+#endif
+constexpr int kEpiWarps = MQ_GEMM_EPI_WARPS;  // 8: thread = row x BN/2 columns (232 regs); 16: row x BN/4 (112 regs)
+constexpr int kColSplit = kEpiWarps / 4;      // column slices of a tile (each TMEM lane quarter has kColSplit warps)
+constexpr int kProducerWarp = kEpiWarps;
+constexpr int kMmaWarp = kEpiWarps + 1;
+constexpr int kAllocWarp = kEpiWarps + 2;
+// + one idle warp: setmaxnreg is a warpgroup-wide instruction, so the issue warps must form a complete group of 4
+// (an 11-warp CTA hung on the B200)
 constexpr int kThreads = (kEpiWarps + 4) * 32;
+constexpr int kEpiRegs = kEpiWarps == 8 ? 232 : 104;  // 16: ptxas launches 608 threads with 96 registers -> 104 after the issue warps shrink to 40
+static_assert(kEpiWarps == 8 || kEpiWarps == 16, "8 or 16 epilogue warps");
 
 struct GemmArgs {
   const float* a_scales;
@@ -124,9 +132,9 @@ mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
                   const __grid_constant__ CUtensorMap map_sa, const __grid_constant__ CUtensorMap map_sw,
                   const GemmArgs p) {
   using L = SmemLayout<BN, kStages>;
-  constexpr int CW = BN / 2;  // columns per epilogue thread
+  constexpr int CW = BN / kColSplit;  // columns per epilogue thread
   constexpr int kTmemCols = 2 * BN;
-  static_assert(CW % 32 == 0, "bad epilogue split");
+  static_assert(CW % 16 == 0, "bad epilogue split");
   static_assert(kTmemCols == 256 || kTmemCols == 512 || kTmemCols == 128, "TMEM columns must be a power of two");
 
   extern __shared__ unsigned char smem_raw[];
@@ -319,7 +327,7 @@ mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
     }
   } else {
     // ------------------------------------------------------------------ epilogue (warps 4..11)
-    reg_alloc<232>();
+    reg_alloc<kEpiRegs>();
     const int ew = warp;
     const int quarter = warp & 3;      // TMEM lane quarter this warp may access
     const int col0 = (ew >> 2) * CW;   // first tile column owned by this thread

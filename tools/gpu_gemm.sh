@@ -1,7 +1,7 @@
 #!/bin/bash
 # GEMM iteration loop: correctness probe, then timings (with the wait-cycle profile) at the 7B prefill shapes
 mkdir -p gpurun_out
-timeout 600 python tools/gemm_probe.py > gpurun_out/gemm_probe.log 2>&1
+timeout 150 python tools/gemm_probe.py > gpurun_out/gemm_probe.log 2>&1
 grep -v '"nbad": 0' gpurun_out/gemm_probe.log | head -5; echo "probe ok cases: $(grep -c '"nbad": 0' gpurun_out/gemm_probe.log) of $(grep -c CASE gpurun_out/gemm_probe.log)"
 export MQ_PROFILE=${MQ_PROFILE-1}
 {
