@@ -170,12 +170,18 @@ def build_stack(layers, tokens, dev, seed, tp=None):
     stack = []
     for _ in range(layers):
         mods = {}
+        # one calibration vector per distinct INPUT tensor: q/k/v see the same hidden state and gate/up the same
+        # attention output, so the reference's hooks give them identical statistics (fake_quant.py:396-455)
+        feat = {src: chan[K] * (1 + 0.05 * torch.rand(K, device=dev, generator=g))
+                for src, K in (("x", HIDDEN), ("attn", HIDDEN), ("o", HIDDEN), ("mlp", INTER))}
+        src_of = {"q_proj": "x", "k_proj": "x", "v_proj": "x", "o_proj": "attn", "gate_proj": "o", "up_proj": "o",
+                  "down_proj": "mlp"}
         for name, (N, K) in SHAPES.items():
             lin = torch.nn.Linear(K, N, bias=False, device=dev, dtype=torch.float16)
             with torch.no_grad():
                 lin.weight.copy_(torch.randn(N, K, device=dev, generator=g) / K ** 0.5)
             # synthetic calibration: importance = mean|x| (run_experiments.py:60), sort key = max|x| (calibration.py:18-25)
-            imp = chan[K] * (1 + 0.05 * torch.rand(K, device=dev, generator=g))
+            imp = feat[src_of[name]]
             mods[name] = W4A4Linear.from_float(lin, "per_group", "per_group", importance=imp.cpu(),
                                                salient_prop=SALIENT, group_size=GROUP, mode="fused",
                                                sort_key=imp * 4.0)

@@ -110,6 +110,29 @@ def quantize_weight_per_group_absmax_sort(w, n_bits, group_size=128, perm=None):
 
 
 # ------------------------------------------------------------------------------------------- the layer
+# One-entry cache of the last quantised activation: (input tensor kept alive, its version, partition id) -> K1 output.
+# Keeping the input alive pins its address, so pointer + version identify its contents (torch ops bump the version;
+# the in-place quantisers of this package bump it explicitly).
+_ACT_CACHE = {"key": None, "x": None, "a": None, "hits": 0}
+
+
+def clear_act_cache():
+    _ACT_CACHE.update(key=None, x=None, a=None)
+
+
+def _shared_act(xin, mod):
+    pid = getattr(mod, "_partition_id", None)
+    key = (xin.data_ptr(), xin._version, tuple(xin.shape), xin.stride(), xin.dtype, xin.device, pid)
+    if pid is not None and _ACT_CACHE["key"] == key:
+        _ACT_CACHE["hits"] += 1
+        return _ACT_CACHE["a"]
+    a = ops.quant_rows(xin, mod.perm, mod.sal_sorted, mod.group_size, mod.quant_bits,
+                       Kn=0 if mod.perm is None else mod.perm.numel())
+    if pid is not None:
+        _ACT_CACHE.update(key=key, x=xin, a=a)
+    return a
+
+
 def _check_choice(value, allowed, what):
     if value not in allowed:
         raise ValueError(f"Invalid {what}: {value}")
@@ -257,8 +280,9 @@ class W4A4Linear(nn.Module):
         cdt = self.w_sal.dtype if self.w_sal is not None else (
             x2.dtype if x2.dtype in (torch.float16, torch.bfloat16) else torch.float16)
         xin = x2 if x2.dtype == cdt else x2.to(cdt)
-        a = ops.quant_rows(xin, self.perm, self.sal_sorted, self.group_size, self.quant_bits,
-                           Kn=0 if self.perm is None else self.perm.numel())
+        # layers fed by the same tensor with the same K partition (q/k/v, gate/up: same calibration statistics in
+        # the reference, fake_quant.py:396-455) share one quantised activation
+        a = _shared_act(xin, self)
         w = ops.QuantizedRows(codes=self.w_codes, scales=self.w_scales, sal=self.w_sal, rows=self.out_features,
                               Kn=a.Kn, Ks=a.Ks, group_size=self.group_size)
         y = ops.mixed_gemm(a, w, self.bias, out_dtype=cdt)
@@ -350,6 +374,10 @@ class W4A4Linear(nn.Module):
         wq = ops.quant_rows(w if w.dtype == cdt else w.to(cdt), perm, sal, self.group_size, self.quant_bits)
         self.perm = perm
         self.w_codes, self.w_scales, self.w_sal = wq.codes, wq.scales, wq.sal
+        import hashlib
+        h = hashlib.sha1(perm.cpu().numpy().tobytes())
+        h.update(b"|" if sal is None else sal.cpu().numpy().tobytes())
+        self._partition_id = (h.hexdigest(), self.group_size, self.quant_bits)
 
     @torch.no_grad()
     def dequantized_weight(self):

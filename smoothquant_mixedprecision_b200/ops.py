@@ -169,6 +169,8 @@ def fakequant_rows(x: torch.Tensor, perm: Optional[torch.Tensor], group_size: in
     with torch.cuda.device(x.device):
         check(lib.mq_fakequant_rows(x2.data_ptr(), R, K, _ld(x2), _dtype_code(x2), _ptr(perm), Kn, int(group_size),
                                     n_bits, out.data_ptr(), _ld(out), _stream(x)), "mq_fakequant_rows")
+    if inplace:
+        torch.autograd.graph.increment_version(x)      # written through a raw pointer: tell torch (and the act cache)
     return x if inplace else out.view(x.shape)
 
 
@@ -183,6 +185,8 @@ def fakequant_tensor(x: torch.Tensor, n_bits: int = 4, inplace: bool = False) ->
     with torch.cuda.device(x.device):
         check(lib.mq_fakequant_tensor(xc.data_ptr(), xc.numel(), _dtype_code(xc), n_bits, out.data_ptr(),
                                       ws.data_ptr(), 16, _stream(x)), "mq_fakequant_tensor")
+    if inplace:
+        torch.autograd.graph.increment_version(x)
     return x if inplace else out.view(x.shape)
 
 

@@ -197,3 +197,36 @@ def test_quantize_model_error_and_key_behaviour(fq):
                                  num_attention_heads=2, max_position_embeddings=32, word_embed_proj_dim=32)).to(DEV)
     with pytest.raises(KeyError):                                                      # no guard in quantize_opt (:396)
         fq.quantize_opt(m, "per_group", "per_group", input_feat={}, salient_prop=0.05)
+
+
+def test_shared_activation_cache_is_transparent(fq):
+    """q/k/v-style layers with the same K partition quantise their common input once; results are identical to
+    quantising per layer, and any change of the input (version bump) or of the partition misses the cache."""
+    torch.manual_seed(11)
+    M, K, g = 96, 512, 128
+    x = (torch.randn(M, K, device=DEV) * torch.exp(0.5 * torch.randn(K, device=DEV))).half()
+    imp = x.abs().float().mean(dim=0).cpu()
+    lins = [nn.Linear(K, n).half().to(DEV) for n in (256, 384)]
+    mods = [fq.W4A4Linear.from_float(l, "per_group", "per_group", importance=imp, salient_prop=0.05, group_size=g,
+                                     mode="fused", sort_key=imp) for l in lins]
+    other = fq.W4A4Linear.from_float(lins[0], "per_group", "per_group", importance=imp.flip(0), salient_prop=0.05,
+                                     group_size=g, mode="fused", sort_key=imp.flip(0))
+    assert mods[0]._partition_id == mods[1]._partition_id != other._partition_id
+    fq.clear_act_cache()
+    ref = []
+    for m in mods:                       # every call misses: cache cleared in between
+        ref.append(m(x).clone())
+        fq.clear_act_cache()
+    h0 = fq._ACT_CACHE["hits"]
+    y0, y1 = mods[0](x), mods[1](x)
+    assert fq._ACT_CACHE["hits"] == h0 + 1
+    assert torch.equal(y0, ref[0]) and torch.equal(y1, ref[1])
+    other(x)                             # different partition: miss, and it replaces the entry
+    assert fq._ACT_CACHE["hits"] == h0 + 1
+    mods[0](x)
+    x.mul_(2)                            # in-place change bumps the version: miss, and the result follows the new data
+    y2 = mods[1](x)
+    assert fq._ACT_CACHE["hits"] == h0 + 1
+    fq.clear_act_cache()
+    assert torch.equal(y2, mods[1](x))
+    fq.clear_act_cache()
