@@ -94,7 +94,12 @@ struct SmemLayout {
   static constexpr int kBarOffset = kScaleOffset + kScaleSlots * kSlotFloats * 4;
   // full[kStages], empty[kStages], tmem_full[2], tmem_empty[2], sfull[kScaleSlots], sempty[kScaleSlots], tmem base
   static constexpr int kBarBytes = (2 * kStages + 4 + 2 * kScaleSlots) * 8 + 16;
-  static constexpr int kTotal = kBarOffset + kBarBytes + 1024;  // + slack to align the base to 1024 bytes
+  // output staging: per epilogue warp 32 rows x 32 columns of 16-bit values, row pitch 80 B (64 + 16: conflict-free
+  // 16-byte accesses both by row and by 8-row x 4-chunk read-back)
+  static constexpr int kOutPitch = 80;
+  static constexpr int kOutWarpBytes = 32 * kOutPitch;
+  static constexpr int kOutOffset = (kBarOffset + kBarBytes + 15) / 16 * 16;
+  static constexpr int kTotal = kOutOffset + kEpiWarps * kOutWarpBytes + 1024;  // + slack to align the base to 1024 B
 };
 
 template <int kRegs>
@@ -466,25 +471,62 @@ mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
         ++uc;
       }
 
-      if (row_ok) {  // bias, rounding, store of this thread's row segment (overlaps the next tile's first MMAs)
-        OutT* yrow = static_cast<OutT*>(p.y) + (int64_t)m * p.ldy + n0 + col0;
+      // ---- bias, rounding, store (overlaps the next tile's first MMAs).  Each thread owns one row, so a direct store
+      // would touch 32 different rows per instruction; instead 32 x 32 slices are transposed through a per-warp
+      // shared-memory buffer and leave as row-contiguous 16-byte chunks (8 rows x 64 B per instruction).
+      {
         const OutT* bias = static_cast<const OutT*>(p.bias);
         const bool vec_ok = (p.ldy % 8 == 0) && (reinterpret_cast<uintptr_t>(p.y) % 16 == 0);
+#ifdef MQ_DEBUG_NOSTORE
+        if (acc[0].x == 1.2345e-30f)
+#endif
+        if (vec_ok) {
+          unsigned char* stg = smem + L::kOutOffset + warp * L::kOutWarpBytes;
+          const int rr = lane >> 2, cc = lane & 3;  // read-back: row within a group of 8, 16-byte chunk within 64 B
 #pragma unroll
-        for (int j8 = 0; j8 < CW / 8; ++j8) {
-          const int n = n0 + col0 + j8 * 8;
-          if (n < p.N) {
-            __align__(16) OutT o[8];
+          for (int sl = 0; sl < CW / 32; ++sl) {
+            const int nb = n0 + col0 + sl * 32;  // first output column of this slice
+            if (nb < p.N) {                       // warp-uniform
 #pragma unroll
-            for (int e = 0; e < 8; ++e) {
-              float r = (e & 1) ? acc[j8 * 4 + e / 2].y : acc[j8 * 4 + e / 2].x;
-              if (bias && n + e < p.N) r += Num<OutT>::to_f(bias[n + e]);
-              o[e] = Num<OutT>::from_f(r);
+              for (int c4 = 0; c4 < 4; ++c4) {
+                __align__(16) OutT o[8];
+#pragma unroll
+                for (int e = 0; e < 8; ++e) {
+                  const float2 av = acc[sl * 16 + c4 * 4 + e / 2];
+                  float r = (e & 1) ? av.y : av.x;
+                  if (bias && nb + c4 * 8 + e < p.N) r += Num<OutT>::to_f(bias[nb + c4 * 8 + e]);
+                  o[e] = Num<OutT>::from_f(r);
+                }
+                *reinterpret_cast<uint4*>(stg + lane * L::kOutPitch + c4 * 16) = *reinterpret_cast<const uint4*>(o);
+              }
+              __syncwarp();
+#pragma unroll
+              for (int it = 0; it < 4; ++it) {
+                const int r = it * 8 + rr;
+                const int gm = m0 + quarter * 32 + r, gn = nb + cc * 8;
+                const uint4 val = *reinterpret_cast<const uint4*>(stg + r * L::kOutPitch + cc * 16);
+                if (gm < p.M && gn < p.N) {
+                  OutT* dst = static_cast<OutT*>(p.y) + (int64_t)gm * p.ldy + gn;
+                  if (gn + 8 <= p.N) {
+                    *reinterpret_cast<uint4*>(dst) = val;
+                  } else {
+                    const OutT* ve = reinterpret_cast<const OutT*>(&val);
+                    for (int e = 0; e < 8 && gn + e < p.N; ++e) dst[e] = ve[e];
+                  }
+                }
+              }
+              __syncwarp();
             }
-            if (vec_ok && n + 8 <= p.N) {
-              *reinterpret_cast<uint4*>(yrow + j8 * 8) = *reinterpret_cast<const uint4*>(o);
-            } else {
-              for (int e = 0; e < 8 && n + e < p.N; ++e) yrow[j8 * 8 + e] = o[e];
+          }
+        } else if (row_ok) {  // unaligned output: element stores straight from the row owner
+          OutT* yrow = static_cast<OutT*>(p.y) + (int64_t)m * p.ldy + n0 + col0;
+#pragma unroll
+          for (int j = 0; j < CW; ++j) {  // fully unrolled: the accumulators must stay in registers
+            const int n = n0 + col0 + j;
+            if (n < p.N) {
+              float r = (j & 1) ? acc[j / 2].y : acc[j / 2].x;
+              if (bias) r += Num<OutT>::to_f(bias[n]);
+              yrow[j] = Num<OutT>::from_f(r);
             }
           }
         }
