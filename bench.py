@@ -257,11 +257,15 @@ def gpu_arm(args):
         step_resident()
     c0 = ops.COUNTERS["launch_calls"]
     ops.GEMM_EVENTS = []
+    ops.QUANT_EVENTS = []
     sampler = ClockSampler(local) if rank == 0 else None
     ms = timed(step_resident, args.steps)
     clocks = sampler.stop() if sampler else None
     launches = (ops.COUNTERS["launch_calls"] - c0) // args.steps
     ev, ops.GEMM_EVENTS = ops.GEMM_EVENTS, None
+    qev, ops.QUANT_EVENTS = ops.QUANT_EVENTS, None
+    quant_ms = sum(a.elapsed_time(b) for a, b, _ in qev) / args.steps
+    quant_bytes = sum(e[2] for e in qev) / args.steps
     gemm_ms = sum(a.elapsed_time(b) for a, b, _, _ in ev) / args.steps
     ops_i8 = sum(e[2] for e in ev) / args.steps
     ops_f16 = sum(e[3] for e in ev) / args.steps
@@ -300,6 +304,12 @@ def gpu_arm(args):
             "roofline": {"kernel": "mixed_gemm_kernel", "bound": "tensor", "achieved": achieved, "peak": peak_mix,
                          "unit": "TOP/s", "frac": achieved / peak_mix, "traffic": None, "peak_source": peak_src,
                          "share_of_step": gemm_ms / ms, "launches_per_step": len(ev) // args.steps},
+            "roofline_quantiser": {"kernel": "quant_rows_fast", "bound": "hbm",
+                                   "achieved": quant_bytes / (quant_ms * 1e-3) / 1e9,
+                                   "peak": peaks.get("hbm_gbs") or 6500.0, "unit": "GB/s",
+                                   "frac": quant_bytes / (quant_ms * 1e-3) / 1e9 / (peaks.get("hbm_gbs") or 6500.0),
+                                   "traffic": None, "share_of_step": quant_ms / ms,
+                                   "launches_per_step": len(qev) // args.steps},
             "clocks": clocks}
     if world == 1 and not args.no_cpu_baseline:
         r = time_cpu(args.cpu_tokens, 2, 1)

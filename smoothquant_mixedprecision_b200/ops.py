@@ -22,6 +22,7 @@ STAT_KINDS = {"max": _lib.MQ_STAT_ABSMAX, "absmax": _lib.MQ_STAT_ABSMAX, "mean":
 # mixed GEMM launch on the launching stream.  Neither synchronises.
 COUNTERS = {"launch_calls": 0}
 GEMM_EVENTS = None          # set to a list to collect (start_event, end_event, ops_int8, ops_f16)
+QUANT_EVENTS = None         # set to a list to collect (start_event, end_event, algorithmic_bytes) per mq_quant_rows
 
 
 def check(rc: int, what: str = "") -> None:
@@ -143,10 +144,19 @@ def quant_rows(x: torch.Tensor, perm: Optional[torch.Tensor], sal: Optional[torc
     sal_out = torch.empty((R, ld_sal), dtype=x2.dtype, device=dev) if Ks > 0 else None
     if smooth is not None:
         smooth = smooth.to(device=dev, dtype=x2.dtype).contiguous()
+    ev = None
+    if QUANT_EVENTS is not None:
+        ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+        ev[0].record(torch.cuda.current_stream(dev))
     with torch.cuda.device(dev):
         check(lib.mq_quant_rows(x2.data_ptr(), R, K, _ld(x2), _dtype_code(x2), _ptr(smooth), _ptr(perm), Kn,
                                 _ptr(sal), Ks, g, n_bits, codes.data_ptr(), ld_codes, scales.data_ptr(), ld_scales,
                                 _ptr(sal_out), ld_sal, _stream(x)), "mq_quant_rows")
+    if ev is not None:
+        ev[1].record(torch.cuda.current_stream(dev))
+        # algorithmic bytes: x read once, codes + fp32 scales + salient copy written once
+        QUANT_EVENTS.append((ev[0], ev[1], R * K * x2.element_size() + R * ld_codes + G * R * 4
+                             + R * ld_sal * x2.element_size()))
     return QuantizedRows(codes=codes, scales=scales[:G], sal=sal_out, rows=R, Kn=Kn, Ks=Ks, group_size=g)
 
 

@@ -188,6 +188,46 @@ def test_fast_and_generic_kernels_agree_at_full_size(ops, mqlib):
     assert mqlib.quant_fault()[0] == 0
 
 
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+def test_division_free_codes_on_rounding_boundaries(ops, mqlib, dtype):
+    """The fast kernel computes round_half_even(rnd_T(x / scale)) without the IEEE divide (remainder-corrected
+    reciprocal multiply).  Adversarial rows: every group holds its abs-max A (so scale = rnd_T(rnd_T(A) / 7)) and
+    values within a few T-ulps of scale * (k + 0.5), i.e. on and around the rounding boundaries where the quotient's
+    rounding to T decides the code.  Must agree bit for bit with the generic kernel (true divide) and the oracle."""
+    g, G, R = 128, 8, 512
+    gen = torch.Generator().manual_seed(5)
+    A = (torch.rand(R, G, generator=gen) * 30 + 0.01).to(dtype)
+    lo = torch.tensor(1e-5, dtype=dtype)
+    scale = (torch.maximum(A, lo) / 7).to(dtype)                      # dtype-local ops like the reference
+    k = torch.randint(-7, 7, (R, G, g), generator=gen).to(torch.float32)
+    x = (scale.float()[:, :, None] * (k + 0.5)).to(dtype)
+    steps = torch.randint(-3, 4, (R, G, g), generator=gen)
+    for _ in range(3):                                                # walk up to 3 ulps either way
+        # step through T's own grid (an fp32 nextafter would round straight back to the same T value)
+        ulp = (x.abs().float() * 2.0 ** (-10 if dtype == torch.float16 else -7)).clamp_min(1e-8)
+        up, dn = (x.float() + ulp).to(dtype), (x.float() - ulp).to(dtype)
+        x = torch.where(steps > 0, up, torch.where(steps < 0, dn, x))
+        steps = steps - steps.sign()
+    x = torch.minimum(torch.maximum(x, -A[:, :, None]), A[:, :, None])
+    x[:, :, 0] = A
+    x2 = x.reshape(R, G * g).to(DEV)
+    a = ops.quant_rows(x2, None, None, g)
+    d = ops.fakequant_rows(x2, None, g)
+    mqlib.set_option("quant_force_generic", 1)
+    try:
+        b = ops.quant_rows(x2, None, None, g)
+        e = ops.fakequant_rows(x2, None, g)
+    finally:
+        mqlib.set_option("quant_force_generic", 0)
+    assert torch.equal(a.codes, b.codes) and torch.equal(a.scales, b.scales)
+    assert torch.equal(d, e)
+    q = O.group_quant(x2.cpu(), 4, g)
+    assert torch.equal(a.codes.cpu()[:, : G * g], q.codes) and torch.equal(d.cpu(), q.deq)
+    # the case is adversarial only if boundary quotients actually occur
+    quot = (x2.cpu().float().view(R, G, g) / q.scales.float().view(R, G, 1)).to(dtype).float()
+    assert int(((quot - quot.floor()) == 0.5).sum()) > 100
+
+
 def test_int4_pack_roundtrip(ops):
     codes = torch.randint(-7, 8, (33, 256), dtype=torch.int8)
     packed = ops.pack_int4(codes.to(DEV))

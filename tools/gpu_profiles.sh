@@ -24,7 +24,7 @@ $GCMD > gpurun_out/plain.log 2>&1 &&
 ncu --set full --clock-control none --import-source on -k regex:mixed_gemm -s 2 -c 1 -f -o gpurun_out/${TAG}_gemm $GCMD \
     > gpurun_out/ncu_gemm.log 2>&1
 echo "ncu gemm rc=$?"
-ncu --set full --clock-control none --import-source on -k regex:quant_rows -s 1 -c 1 -f -o gpurun_out/${TAG}_quant $GCMD \
+ncu --set full --clock-control none --import-source on -k regex:quant_rows -s 0 -c 1 -f -o gpurun_out/${TAG}_quant $GCMD \
     > gpurun_out/ncu_quant.log 2>&1
 echo "ncu quant rc=$?"
 ls -la gpurun_out/ | tail -20
