@@ -90,6 +90,20 @@ int mq_quant_rows(const void* x, int64_t R, int64_t K, int64_t ld, int dtype, co
                   int8_t* out_codes, int64_t ld_codes, float* out_scales, int64_t ld_scales,
                   void* out_sal, int64_t ld_sal, void* stream);
 
+/* Hybrid split of the same quantiser: the first `int_groups` groups leave as integer codes + scales exactly as above
+ * (for the tcgen05 kind::i8 units of mq_mixed_gemm), the remaining groups leave DEQUANTISED -- code * scale rounded to
+ * dtype, i.e. the very values quantize_*_per_group_absmax returns (fake_quant.py:97, :49) -- in out_sal columns
+ * [t0, t0 + (G - int_groups) * group_size), t0 = Ks rounded up to 8, where mq_mixed_gemm contracts them together with
+ * the salient columns as kind::f16 MMAs.  The per-group rescale of the integer units runs on the CUDA cores and
+ * bounds the GEMM for group sizes <= 128; moving part of K to the 16-bit tensor path balances the two pipes
+ * (DESIGN.md 3).  Needs ld_codes >= int_groups*group_size and ld_sal >= t0 + (G - int_groups)*group_size.
+ * int_groups == G is mq_quant_rows. */
+int mq_quant_rows_split(const void* x, int64_t R, int64_t K, int64_t ld, int dtype, const void* smooth,
+                        const int32_t* perm, int64_t Kn, const int32_t* sal, int64_t Ks,
+                        int group_size, int n_bits, int64_t int_groups,
+                        int8_t* out_codes, int64_t ld_codes, float* out_scales, int64_t ld_scales,
+                        void* out_sal, int64_t ld_sal, void* stream);
+
 /* Same arithmetic, reference-shaped output: out [R, K] (dtype) holds code*scale at the ORIGINAL column of every
  * permuted position and x itself at every column not listed in perm (salient pass-through).
  *     Replaces  quantize_activation_per_group_absmax_sort   fake_quant.py:105-154  (perm = argsort of the key)

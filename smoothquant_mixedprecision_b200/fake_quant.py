@@ -120,6 +120,28 @@ def clear_act_cache():
     _ACT_CACHE.update(key=None, x=None, a=None)
 
 
+# Share of the K groups that run as integer codes (tcgen05 kind::i8 + per-group fp32 rescale on the CUDA cores); the
+# rest leave the quantiser DEQUANTISED (code * scale rounded to the 16-bit type, the reference's fake-quantised value)
+# and run through the 16-bit tensor path together with the salient columns.  The rescale bounds the integer path for
+# small groups.  Measured on a B200 at 32768 x 4096 x 4096, 5 % salient (profiles/r01_hybrid_sweep.txt):
+# g = 64: 1.46 ms all-integer, 0.88 ms all-dequantised, monotone in between; g = 128: 0.83 ms all-integer, 0.80 ms at
+# 0.7 (but the quantiser then writes 2-byte tails and K = 11008 loses), 0.89 ms all-dequantised; g = 256: all-integer
+# wins everywhere.  So groups below 128 default to the 16-bit path (the packed weight then holds 2 bytes per
+# element; pass int_fraction=1.0 to keep 1-byte codes, e.g. for weight-stream-bound decode), 128 and up to integers.
+def default_int_fraction(g):
+    return 0.0 if g < 128 else 1.0
+
+
+def _int_groups(G, g, frac):
+    if frac is None:
+        frac = default_int_fraction(g)
+    if not 0.0 <= frac <= 1.0:
+        raise ValueError(f"int_fraction must be in [0, 1], got {frac}")
+    step = max(1, 128 // g)                 # the integer part must fill whole 128-column K blocks
+    gi = int(round(G * frac)) // step * step
+    return max(0, min(G, gi))
+
+
 def _shared_act(xin, mod):
     pid = getattr(mod, "_partition_id", None)
     key = (xin.data_ptr(), xin._version, tuple(xin.shape), xin.stride(), xin.dtype, xin.device, pid)
@@ -127,7 +149,7 @@ def _shared_act(xin, mod):
         _ACT_CACHE["hits"] += 1
         return _ACT_CACHE["a"]
     a = ops.quant_rows(xin, mod.perm, mod.sal_sorted, mod.group_size, mod.quant_bits,
-                       Kn=0 if mod.perm is None else mod.perm.numel())
+                       Kn=0 if mod.perm is None else mod.perm.numel(), int_groups=mod.int_groups)
     if pid is not None:
         _ACT_CACHE.update(key=key, x=xin, a=a)
     return a
@@ -169,6 +191,8 @@ class W4A4Linear(nn.Module):
         # fused-mode operands (filled by from_float)
         for name in ("w_codes", "w_scales", "w_sal", "perm", "sal_sorted", "keep"):
             self.register_buffer(name, None)
+        self.int_groups = None              # fused mode: groups kept as integer codes (hybrid engine), set by the packer
+        self.int_fraction = None
         self.salient_indices = None
         self.tp_rank, self.tp_world, self.tp_group, self.tp_gather_output = 0, 1, None, True
         self.full_out_features = out_features
@@ -284,7 +308,7 @@ class W4A4Linear(nn.Module):
         # the reference, fake_quant.py:396-455) share one quantised activation
         a = _shared_act(xin, self)
         w = ops.QuantizedRows(codes=self.w_codes, scales=self.w_scales, sal=self.w_sal, rows=self.out_features,
-                              Kn=a.Kn, Ks=a.Ks, group_size=self.group_size)
+                              Kn=a.Kn, Ks=a.Ks, group_size=self.group_size, int_groups=a.int_groups)
         y = ops.mixed_gemm(a, w, self.bias, out_dtype=cdt)
         if self.output_quant_name != "None":
             y = self._quantize_output(y)
@@ -323,7 +347,7 @@ class W4A4Linear(nn.Module):
     @torch.no_grad()
     def from_float(module, weight_quant="per_channel", act_quant="per_token", quantize_output=False, importance=None,
                    salient_prop=0, quant_bits=4, group_size=128, mode="reference", sort="max", sort_key=None,
-                   weight_perm=None, tp_group=None, tp_gather_output=True):
+                   weight_perm=None, tp_group=None, tp_gather_output=True, int_fraction=None):
         assert isinstance(module, torch.nn.Linear)                                    # fake_quant.py:335
         _check_choice(weight_quant, _WEIGHT_QUANTS, "weight_quant")                   # ValueError, fake_quant.py:361
         w = module.weight.data
@@ -339,6 +363,7 @@ class W4A4Linear(nn.Module):
         if mode == "fused":
             if weight_quant != "per_group" or act_quant != "per_group":
                 raise ValueError("mode='fused' needs weight_quant='per_group' and act_quant='per_group'")
+            new.int_fraction = int_fraction
             new._pack_fused(w, sort_key if sort_key is not None else importance)
         else:
             if weight_quant == "per_group":       # sorts ALL K columns by the weight's own abs-max (:164-167)
@@ -371,13 +396,16 @@ class W4A4Linear(nn.Module):
             key = torch.as_tensor(key).to(device=dev, dtype=torch.float32)
             perm = ops.argsort_stable(key, subset=keep)
         cdt = w.dtype if w.dtype in (torch.float16, torch.bfloat16) else torch.float16
-        wq = ops.quant_rows(w if w.dtype == cdt else w.to(cdt), perm, sal, self.group_size, self.quant_bits)
+        G = (perm.numel() + self.group_size - 1) // self.group_size
+        self.int_groups = _int_groups(G, self.group_size, self.int_fraction)
+        wq = ops.quant_rows(w if w.dtype == cdt else w.to(cdt), perm, sal, self.group_size, self.quant_bits,
+                            int_groups=self.int_groups)
         self.perm = perm
         self.w_codes, self.w_scales, self.w_sal = wq.codes, wq.scales, wq.sal
         import hashlib
         h = hashlib.sha1(perm.cpu().numpy().tobytes())
         h.update(b"|" if sal is None else sal.cpu().numpy().tobytes())
-        self._partition_id = (h.hexdigest(), self.group_size, self.quant_bits)
+        self._partition_id = (h.hexdigest(), self.group_size, self.quant_bits, self.int_groups)
 
     @torch.no_grad()
     def dequantized_weight(self):
@@ -386,21 +414,28 @@ class W4A4Linear(nn.Module):
         N, K, g = self.out_features, self.in_features, self.group_size
         Kn = self.perm.numel()
         G = (Kn + g - 1) // g
+        Gi = G if self.int_groups is None else self.int_groups
         dt = self.w_sal.dtype if self.w_sal is not None else torch.float16
         out = torch.zeros((N, K), dtype=dt, device=self.w_codes.device)
+        ks = 0 if self.sal_sorted is None else self.sal_sorted.numel()
         if Kn:
-            sc = self.w_scales[:G, :N].t().to(dt)                                      # exact: scales are dt values
-            deq = (self.w_codes[:, : G * g].view(N, G, g).to(dt) * sc[:, :, None]).view(N, G * g)[:, :Kn]
-            out[:, self.perm.long()] = deq
-        if self.sal_sorted is not None:
-            out[:, self.sal_sorted.long()] = self.w_sal[:, : self.sal_sorted.numel()]
+            deq = torch.zeros((N, G * g), dtype=dt, device=out.device)
+            if Gi:
+                sc = self.w_scales[:Gi, :N].t().to(dt)                                 # exact: scales are dt values
+                deq[:, : Gi * g] = (self.w_codes[:, : Gi * g].view(N, Gi, g).to(dt) * sc[:, :, None]).view(N, Gi * g)
+            if Gi < G:                                                                 # hybrid tail: stored dequantised
+                t0 = (ks + 7) // 8 * 8
+                deq[:, Gi * g:] = self.w_sal[:, t0: t0 + (G - Gi) * g]
+            out[:, self.perm.long()] = deq[:, :Kn]
+        if ks:
+            out[:, self.sal_sorted.long()] = self.w_sal[:, :ks]
         return out
 
     def packed_bytes(self) -> int:
         """True storage of the layer (the reference's get_model_size stops counting quantised linears)."""
         if self.mode == "fused" and self.w_codes is not None:
-            Kn = self.perm.numel()
-            n = self.out_features * ((Kn + 1) // 2) + self.w_scales.numel() * 2
+            Kn = self.perm.numel()      # at rest every quantised column is an int4 nibble + one 16-bit scale per group
+            n = self.out_features * ((Kn + 1) // 2) + self.out_features * ((Kn + self.group_size - 1) // self.group_size) * 2
             if self.w_sal is not None:
                 n += self.out_features * self.sal_sorted.numel() * self.w_sal.element_size()
             n += Kn * 4
@@ -431,7 +466,8 @@ def _swap(parent, attr, prefix, input_feat, guarded, quantize_output, kw, extra)
     setattr(parent, attr, W4A4Linear.from_float(
         getattr(parent, attr), quantize_output=quantize_output, importance=imp,
         sort_key=None if sk is None else sk.get(prefix + "." + attr),
-        mode=extra.get("mode", "reference"), sort=extra.get("sort", "max"), tp_group=extra.get("tp_group"), **kw))
+        mode=extra.get("mode", "reference"), sort=extra.get("sort", "max"), tp_group=extra.get("tp_group"),
+        int_fraction=extra.get("int_fraction"), **kw))
 
 
 def quantize_opt(model, weight_quant="per_tensor", act_quant="per_tensor", quantize_bmm_input=True, input_feat=None,

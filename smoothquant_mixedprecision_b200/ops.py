@@ -110,21 +110,26 @@ class QuantizedRows:
     """Output of the fused row quantiser: what the mixed GEMM consumes for one operand."""
     codes: torch.Tensor            # int8  [R, ld_codes]  codes in [-qmax, qmax], zero beyond Kn
     scales: torch.Tensor           # fp32  [G, ld_scales] group-major
-    sal: Optional[torch.Tensor]    # dtype [R, ld_sal]    salient columns (zero padded), None if Ks == 0
+    sal: Optional[torch.Tensor]    # dtype [R, ld_sal]    salient columns (zero padded) [+ dequantised tail groups]
     rows: int
     Kn: int
-    Ks: int
+    Ks: int                        # columns of `sal` the 16-bit MMA contracts (salient, pad to 8, hybrid tail)
     group_size: int
+    int_groups: Optional[int] = None   # groups held as integer codes (None: all of them)
+    n_salient: Optional[int] = None    # true salient column count (Ks when there is no hybrid tail)
 
     @property
     def groups(self) -> int:
-        return self.scales.shape[0]
+        return self.scales.shape[0] if self.int_groups is None else self.int_groups
 
 
 def quant_rows(x: torch.Tensor, perm: Optional[torch.Tensor], sal: Optional[torch.Tensor], group_size: int,
-               n_bits: int = 4, smooth: Optional[torch.Tensor] = None, Kn: Optional[int] = None) -> QuantizedRows:
+               n_bits: int = 4, smooth: Optional[torch.Tensor] = None, Kn: Optional[int] = None,
+               int_groups: Optional[int] = None) -> QuantizedRows:
     """codes/scales of x[:, perm] per group of ``group_size`` plus the salient columns x[:, sal] in x's dtype.
-    perm=None means the identity over the first Kn columns (fake_quant.py:78-101 / :30-53 on x[:, perm])."""
+    perm=None means the identity over the first Kn columns (fake_quant.py:78-101 / :30-53 on x[:, perm]).
+    ``int_groups`` < G (hybrid engine): only the first ``int_groups`` groups leave as codes, the rest leave
+    dequantised behind the salient columns of ``sal`` (mq_quant_rows_split)."""
     _need_cuda(x, perm, sal, smooth)
     x2 = _rows2d(x)
     R, K = x2.shape
@@ -136,12 +141,19 @@ def quant_rows(x: torch.Tensor, perm: Optional[torch.Tensor], sal: Optional[torc
     Ks = 0 if sal is None else sal.numel()
     g = int(group_size)
     G = (Kn + g - 1) // g
-    ld_codes = max(_round_up(G * g, 128), 128)
+    Gi = G if int_groups is None else int(int_groups)
+    if not 0 <= Gi <= G:
+        raise ValueError(f"int_groups={Gi} outside [0, {G}]")
+    tail = (G - Gi) * g
+    if tail and x2.dtype not in (torch.float16, torch.bfloat16):
+        raise TypeError("the hybrid tail is stored in the 16-bit compute dtype; cast the input first")
+    ld_codes = max(_round_up(Gi * g, 128), 128)
     ld_scales = max(_round_up(R, 4), 4)
-    ld_sal = _round_up(Ks, 8)
+    ks_total = (_round_up(Ks, 8) + tail) if tail else Ks
+    ld_sal = _round_up(ks_total, 8)
     codes = torch.empty((R, ld_codes), dtype=torch.int8, device=dev)
-    scales = torch.empty((max(G, 1), ld_scales), dtype=torch.float32, device=dev)
-    sal_out = torch.empty((R, ld_sal), dtype=x2.dtype, device=dev) if Ks > 0 else None
+    scales = torch.empty((max(Gi, 1), ld_scales), dtype=torch.float32, device=dev)
+    sal_out = torch.empty((R, ld_sal), dtype=x2.dtype, device=dev) if ks_total > 0 else None
     if smooth is not None:
         smooth = smooth.to(device=dev, dtype=x2.dtype).contiguous()
     ev = None
@@ -149,15 +161,16 @@ def quant_rows(x: torch.Tensor, perm: Optional[torch.Tensor], sal: Optional[torc
         ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
         ev[0].record(torch.cuda.current_stream(dev))
     with torch.cuda.device(dev):
-        check(lib.mq_quant_rows(x2.data_ptr(), R, K, _ld(x2), _dtype_code(x2), _ptr(smooth), _ptr(perm), Kn,
-                                _ptr(sal), Ks, g, n_bits, codes.data_ptr(), ld_codes, scales.data_ptr(), ld_scales,
-                                _ptr(sal_out), ld_sal, _stream(x)), "mq_quant_rows")
+        check(lib.mq_quant_rows_split(x2.data_ptr(), R, K, _ld(x2), _dtype_code(x2), _ptr(smooth), _ptr(perm), Kn,
+                                      _ptr(sal), Ks, g, n_bits, Gi, codes.data_ptr(), ld_codes, scales.data_ptr(),
+                                      ld_scales, _ptr(sal_out), ld_sal, _stream(x)), "mq_quant_rows_split")
     if ev is not None:
         ev[1].record(torch.cuda.current_stream(dev))
         # algorithmic bytes: x read once, codes + fp32 scales + salient copy written once
-        QUANT_EVENTS.append((ev[0], ev[1], R * K * x2.element_size() + R * ld_codes + G * R * 4
+        QUANT_EVENTS.append((ev[0], ev[1], R * K * x2.element_size() + R * Gi * g + Gi * R * 4
                              + R * ld_sal * x2.element_size()))
-    return QuantizedRows(codes=codes, scales=scales[:G], sal=sal_out, rows=R, Kn=Kn, Ks=Ks, group_size=g)
+    return QuantizedRows(codes=codes, scales=scales[:Gi], sal=sal_out, rows=R, Kn=Kn, Ks=ks_total, group_size=g,
+                         int_groups=Gi, n_salient=Ks)
 
 
 def fakequant_rows(x: torch.Tensor, perm: Optional[torch.Tensor], group_size: int, n_bits: int = 4,
@@ -239,7 +252,7 @@ def mixed_gemm(a: Optional[QuantizedRows], w: Optional[QuantizedRows], bias: Opt
         if Ks is None:
             Ks = a.Ks
         M, N, G, g = a.rows, w.rows, a.groups if a.Kn > 0 else 0, a.group_size
-        if G != (w.groups if w.Kn > 0 else 0) or (G > 0 and g != w.group_size):
+        if G != (w.groups if w.Kn > 0 else 0) or (G > 0 and g != w.group_size) or a.Ks != w.Ks:
             raise ValueError("activation / weight group partitions differ")
         dev = a.codes.device
     else:

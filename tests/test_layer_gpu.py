@@ -92,8 +92,12 @@ def test_reference_mode_dynamic_sort_matches_oracle(fq, golden_layers):
     assert n >= 1
 
 
+@pytest.mark.parametrize("int_fraction", [1.0, None, 0.5, 0.0])
 @pytest.mark.parametrize("sort", ["max", "mean3std", "argmax", "none"])
-def test_fused_mode_layer_matches_composed_oracle(fq, golden_layers, sort):
+def test_fused_mode_layer_matches_composed_oracle(fq, golden_layers, sort, int_fraction):
+    """int_fraction selects the engine split: 1.0 all groups as integer codes, 0.0 all groups dequantised on the 16-bit
+    tensor path, None the measured default for the group size.  Whatever the split, the packed weight holds the
+    oracle's codes / scales for the integer groups and the oracle's dequantised values for the rest, bit for bit."""
     for c in golden_layers:
         if c["act_quant"] != "per_group" or c["quantize_output"]:
             continue
@@ -102,7 +106,7 @@ def test_fused_mode_layer_matches_composed_oracle(fq, golden_layers, sort):
         key = None if sort == "none" else O.sort_key(x2, sort).float()
         mod = fq.W4A4Linear.from_float(_linear_from(c), "per_group", "per_group",
                                        importance=c["importance"] if p > 0 else None, salient_prop=p, group_size=g,
-                                       mode="fused", sort=sort, sort_key=key)
+                                       mode="fused", sort=sort, sort_key=key, int_fraction=int_fraction)
         part = O.fused_partition(K, c["salient_indices"], key, g)
         xo, wo = x2, c["weight_fp"]
         if xo.dtype == torch.float32:          # fused mode computes in fp16: the oracle sees the same cast
@@ -110,8 +114,13 @@ def test_fused_mode_layer_matches_composed_oracle(fq, golden_layers, sort):
         y64, aq, wq = O.fused_layer_oracle(xo, wo, c["bias"], part)
         assert torch.equal(mod.perm.cpu().long(), part.perm)
         G = aq.scales.shape[1]
-        assert torch.equal(mod.w_codes.cpu()[:, : G * g], wq.codes)                   # bit-exact codes
-        assert torch.equal(mod.w_scales.cpu()[:, : c["N"]].t(), wq.scales.float())    # bit-exact scales
+        Gi, ks = mod.int_groups, part.salient.numel()
+        assert 0 <= Gi <= G and (int_fraction != 1.0 or Gi == G) and (int_fraction != 0.0 or Gi == 0)
+        assert torch.equal(mod.w_codes.cpu()[:, : Gi * g], wq.codes[:, : Gi * g])                   # bit-exact codes
+        assert torch.equal(mod.w_scales.cpu()[:Gi, : c["N"]].t(), wq.scales.float()[:, :Gi])        # bit-exact scales
+        if Gi < G:                                     # 16-bit tail behind the salient columns: the fake-quant value
+            t0, n = (ks + 7) // 8 * 8, wq.deq.shape[1] - Gi * g
+            assert torch.equal(mod.w_sal.cpu()[:, t0: t0 + n], wq.deq[:, Gi * g:].to(mod.w_sal.dtype))
         y = mod(c["x"].to(DEV)).reshape(-1, c["N"]).double().cpu()
         tol = (8e-3 if xo.dtype == torch.bfloat16 else 1e-3) * float(y64.abs().max()) + 1e-3
         assert float((y - y64).abs().max()) <= tol

@@ -312,3 +312,50 @@ def test_pure_f16_gemm_reference_mode(ops):
     y = ops.mixed_gemm(None, None, b, a_sal=a, w_sal=w)
     ref = a.float() @ w.float().t() + b.float()
     assert float((y.float() - ref).abs().max()) <= 2e-3 * float(ref.abs().max())
+
+
+@pytest.mark.parametrize("g,Gi", [(128, 0), (128, 3), (128, 7), (64, 4), (64, 3), (32, 8), (32, 5)])
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+def test_hybrid_split_tail_is_the_reference_dequantised_value(ops, mqlib, g, Gi, dtype):
+    """mq_quant_rows_split: the first Gi groups are the integer codes / scales of the plain quantiser, the remaining
+    groups are bit for bit the fake-quantised (dequantised) values the reference quantiser returns, laid out behind
+    the salient columns; fast and generic kernels agree; the mixed GEMM on the split operands matches the composed
+    float64 reference."""
+    M, K, N, ks = 160, 1024, 192, 51
+    x = synth(M, K, dtype, 21).to(DEV)
+    w = (torch.randn(N, K, generator=torch.Generator().manual_seed(4)) * 0.05).to(dtype).to(DEV)
+    order = torch.randperm(K, generator=torch.Generator().manual_seed(2))
+    perm, sal = order[ks:].to(DEV), torch.sort(order[:ks]).values.to(DEV)
+    Kn = K - ks
+    G = (Kn + g - 1) // g
+    full = ops.quant_rows(x, perm, sal, g)
+    deq = ops.fakequant_rows(x, perm, g)                      # == quantize_activation_per_group_absmax on x[:, perm]
+    a = ops.quant_rows(x, perm, sal, g, int_groups=Gi)
+    mqlib.set_option("quant_force_generic", 1)
+    try:
+        a_gen = ops.quant_rows(x, perm, sal, g, int_groups=Gi)
+    finally:
+        mqlib.set_option("quant_force_generic", 0)
+    t0, tail = (ks + 7) // 8 * 8, (G - Gi) * g
+    assert a.Ks == t0 + tail and a.groups == Gi and a.n_salient == ks
+    if Gi:
+        assert torch.equal(a.codes[:, : Gi * g], full.codes[:, : Gi * g]) and torch.equal(a.scales, full.scales[:Gi])
+        assert torch.equal(a.codes[:, : Gi * g], a_gen.codes[:, : Gi * g]) and torch.equal(a.scales, a_gen.scales)
+    assert torch.equal(a.sal[:, :ks], full.sal[:, :ks]) and not a.sal[:, ks:t0].any()
+    want_tail = torch.zeros(M, tail, dtype=dtype, device=DEV)
+    cols = perm[Gi * g:].long()
+    want_tail[:, : cols.numel()] = deq[:, cols]
+    assert torch.equal(a.sal[:, t0: t0 + tail], want_tail)
+    assert torch.equal(a.sal[:, : t0 + tail], a_gen.sal[:, : t0 + tail])
+    wq = ops.quant_rows(w, perm, sal, g, int_groups=Gi)
+    y = ops.mixed_gemm(a, wq, None)
+    wfull = ops.quant_rows(w, perm, sal, g)
+    Gg = G * g
+    ad = (full.codes[:, :Gg].double().view(M, G, g) * full.scales[:G, :M].t().double()[:, :, None]).view(M, Gg)
+    wd = (wfull.codes[:, :Gg].double().view(N, G, g) * wfull.scales[:G, :N].t().double()[:, :, None]).view(N, Gg)
+    ref = ad @ wd.t() + full.sal[:, :ks].double() @ wfull.sal[:, :ks].double().t()
+    err = float((y.double() - ref).abs().max())
+    # fp16 / bf16 rounding of the output and of the tail operands (2^-11 / 2^-8 relative), written as a bound
+    tol = (2e-3 if dtype == torch.float16 else 1.6e-2) * float(ref.abs().max()) + 1e-3
+    assert err <= tol, (err, tol)
+    assert mqlib.gemm_fault()[0] == 0 and mqlib.quant_fault()[0] == 0

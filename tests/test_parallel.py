@@ -96,9 +96,9 @@ def test_column_shards_reproduce_unsharded_layer(world):
     lin = torch.nn.Linear(K, N).half().cuda()
     x = (torch.randn(M, K, device="cuda") * torch.exp(0.5 * torch.randn(K, device="cuda"))).half()
     imp = x.abs().float().mean(dim=0).cpu()
-    for mode in ("fused", "reference"):
+    for mode, frac in (("fused", 1.0), ("fused", 0.5), ("fused", 0.0), ("reference", None)):
         full = W4A4Linear.from_float(lin, "per_group", "per_group", importance=imp, salient_prop=0.05, group_size=g,
-                                     mode=mode, sort_key=imp)
+                                     mode=mode, sort_key=imp, int_fraction=frac)
         perm = None
         if mode == "reference":                       # freeze the dynamic permutation so that every shard shares it
             from smoothquant_mixedprecision_b200 import fake_quant as fq

@@ -17,8 +17,12 @@ order = torch.randperm(K, device=dev)
 ks = max(1, int(p * K)) if p > 0 else 0
 perm = order[ks:].int()
 sal = torch.sort(order[:ks]).values.int() if ks else None
-a = ops.quant_rows(x, perm, sal, g)
-wq = ops.quant_rows(w, perm, sal, g)
+frac = float(os.environ.get("MQ_INT_FRACTION", "1.0"))       # hybrid engine: share of the groups kept as integer codes
+G = (perm.numel() + g - 1) // g
+step = max(1, 128 // g)
+gi = max(0, min(G, int(round(G * frac)) // step * step))
+a = ops.quant_rows(x, perm, sal, g, int_groups=gi)
+wq = ops.quant_rows(w, perm, sal, g, int_groups=gi)
 _lib.set_option("gemm_debug", debug)
 if debug:
     _lib.set_option("gemm_profile", 1)      # the debug bits live in the profiling variant of the kernel
@@ -42,5 +46,5 @@ if os.environ.get("MQ_PROFILE"):
     med["clock_ghz"] = med["cycles"] / max(med["ns"], 1)
     print("PROF " + json.dumps(med), flush=True)
     _lib.set_option("gemm_profile", 0)
-print("GEMM " + json.dumps(dict(M=M, N=N, K=K, g=g, p=p, debug=debug, ms=ms, tops=2.0 * M * N * K / ms / 1e9,
+print("GEMM " + json.dumps(dict(M=M, N=N, K=K, g=g, p=p, int_groups=gi, groups=G, debug=debug, ms=ms, tops=2.0 * M * N * K / ms / 1e9,
                                 fault=_lib.gemm_fault()[:5])), flush=True)
