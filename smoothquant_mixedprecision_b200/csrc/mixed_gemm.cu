@@ -73,6 +73,9 @@ struct GemmArgs {
 #define MQ_GEMM_PRELOAD 1
 #endif
 constexpr bool kPreload = MQ_GEMM_PRELOAD != 0;
+#ifndef MQ_GEMM_PAIR_DEFAULT
+#define MQ_GEMM_PAIR_DEFAULT 2  // 1: CTA-pair kernel whenever BN = 256 and M > 128;  2: single-CTA kernel
+#endif
 constexpr int kScaleSlots = 8;  // ring of per-unit scale vectors (ws[BN] | as[BM], fp32) staged in shared memory by TMA
 
 // optional per-CTA wait-cycle profile (option gemm_profile): 8 x u64 per CTA
@@ -83,10 +86,13 @@ constexpr int kProfSlots = 8;
 constexpr int kProfCtas = 256;
 __device__ unsigned long long g_gemm_prof[kProfCtas * kProfSlots];
 
-template <int BN, int kStages>
+// kPair: CTA-pair kernel (cta_group::2, a 256 x BN tile per pair): each CTA stages its own 128 rows of A and HALF of
+// the W tile per K block, so that the L2 -> shared-memory operand stream per SM drops by a third.
+template <int BN, int kStages, bool kPair = false>
 struct SmemLayout {
   static constexpr int kABytes = BM * kKBlockBytes;
-  static constexpr int kBBytes = BN * kKBlockBytes;
+  static constexpr int kBRows = kPair ? BN / 2 : BN;  // W rows staged by this CTA
+  static constexpr int kBBytes = kBRows * kKBlockBytes;
   static constexpr int kStageBytes = kABytes + kBBytes;
   // per scale slot: ws[BN] | as[BM]   (fp32)
   static constexpr int kSlotFloats = BN + BM;
@@ -100,6 +106,7 @@ struct SmemLayout {
   static constexpr int kOutWarpBytes = 32 * kOutPitch;
   static constexpr int kOutOffset = (kBarOffset + kBarBytes + 15) / 16 * 16;
   static constexpr int kTotal = kOutOffset + kEpiWarps * kOutWarpBytes + 1024;  // + slack to align the base to 1024 B
+  static_assert(kTotal <= 232448, "shared memory budget");
 };
 
 template <int kRegs>
@@ -130,14 +137,20 @@ __device__ __forceinline__ long long wait_timed(bool prof, uint32_t bar, uint32_
   return ok ? clock64() - t : -1;
 }
 
-template <typename OutT, int BN, int kStages, bool kProf>
+template <typename OutT, int BN, int kStages, bool kProf, bool kPair>
 __global__ void __launch_bounds__(kThreads, 1)
 mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_w,
                   const __grid_constant__ CUtensorMap map_as, const __grid_constant__ CUtensorMap map_ws,
                   const __grid_constant__ CUtensorMap map_sa, const __grid_constant__ CUtensorMap map_sw,
                   const GemmArgs p) {
-  using L = SmemLayout<BN, kStages>;
+  using L = SmemLayout<BN, kStages, kPair>;
   constexpr int CW = BN / kColSplit;  // columns per epilogue thread
+  // work distribution: a CTA (or a CTA pair) loops over 128 (256) x BN tiles; `wid` / `wstride` index the workers
+  const uint32_t cta_rank = kPair ? cluster_ctarank() : 0u;
+  const bool leader = cta_rank == 0u;
+  const int wid = kPair ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
+  const int wstride = kPair ? (int)(gridDim.x >> 1) : (int)gridDim.x;
+  constexpr int TM = kPair ? 2 * BM : BM;  // tile rows per worker
   constexpr int kTmemCols = 2 * BN;
   static_assert(CW % 16 == 0, "bad epilogue split");
   static_assert(kTmemCols == 256 || kTmemCols == 512 || kTmemCols == 128, "TMEM columns must be a power of two");
@@ -178,7 +191,7 @@ mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
     }
     for (int t = 0; t < 2; ++t) {
       mbar_init(&tfull_bar[t], 1);
-      mbar_init(&tempty_bar[t], kEpiWarps);
+      mbar_init(&tempty_bar[t], kPair ? 2 * kEpiWarps : kEpiWarps);  // pair: the epilogues of both CTAs
     }
     for (int s = 0; s < kScaleSlots; ++s) {
       mbar_init(&sfull_bar[s], 1);
@@ -186,9 +199,13 @@ mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
     }
     fence_mbar_init();
   }
-  if (warp == kAllocWarp) tmem_alloc<kTmemCols>(tmem_slot);
+  if (warp == kAllocWarp) {
+    if (kPair) tmem_alloc_pair<kTmemCols>(tmem_slot);
+    else tmem_alloc<kTmemCols>(tmem_slot);
+  }
   tc_fence_before();
-  __syncthreads();
+  if (kPair) cluster_sync_all();  // barriers of both CTAs initialised before any remote arrive / multicast commit
+  else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(tmem_slot);
 
@@ -200,8 +217,10 @@ mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
     if (warp == kProducerWarp) {
       // ------------------------------------------------------------------ TMA producer
       uint32_t kbc = 0, sc = 0;  // K blocks / scale slots issued so far (ring positions)
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-        const int m0 = (tile / p.tiles_n) * BM, n0 = (tile % p.tiles_n) * BN;
+      const uint32_t full_leader = kPair ? mapa_u32(smem_u32(full_bar), 0u) : 0u;
+      for (int tile = wid; tile < num_tiles; tile += wstride) {
+        const int m0 = (tile / p.tiles_n) * TM + (int)cta_rank * BM, n0 = (tile % p.tiles_n) * BN;
+        const int nw = n0 + (int)cta_rank * L::kBRows;  // first W row this CTA stages
         int u_next = 0;  // next integer unit whose scale vectors have not been requested yet
         for (int kb = 0; kb < kb_total; ++kb, ++kbc) {
           // scale vectors of every unit that starts inside this K block: ws[u, n0 .. n0+BN) and as[u, m0 .. m0+BM)
@@ -223,24 +242,42 @@ mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
           unsigned char* sa = smem + (size_t)s * L::kStageBytes;
           unsigned char* sb = sa + L::kABytes;
           if (elect_one()) {
-            mbar_expect_tx(&full_bar[s], (uint32_t)L::kStageBytes);
-            if (kb < p.kb_int) {
-              tma_load_2d(sa, &map_a, kb * 128, m0, &full_bar[s]);
-              tma_load_2d(sb, &map_w, kb * 128, n0, &full_bar[s]);
+            if (kPair) {  // both CTAs' bytes complete on the leader's barrier, which the leader arms for both
+              if (leader) mbar_expect_tx(&full_bar[s], (uint32_t)(2 * L::kStageBytes));
+              const uint32_t fb = full_leader + s * 8u;
+              if (kb < p.kb_int) {
+                tma_load_2d_pair(sa, &map_a, kb * 128, m0, fb);
+                tma_load_2d_pair(sb, &map_w, kb * 128, nw, fb);
+              } else {
+                const int ks = (kb - p.kb_int) * 64;
+                tma_load_2d_pair(sa, &map_as, ks, m0, fb);
+                tma_load_2d_pair(sb, &map_ws, ks, nw, fb);
+              }
             } else {
-              const int ks = (kb - p.kb_int) * 64;
-              tma_load_2d(sa, &map_as, ks, m0, &full_bar[s]);
-              tma_load_2d(sb, &map_ws, ks, n0, &full_bar[s]);
+              mbar_expect_tx(&full_bar[s], (uint32_t)L::kStageBytes);
+              if (kb < p.kb_int) {
+                tma_load_2d(sa, &map_a, kb * 128, m0, &full_bar[s]);
+                tma_load_2d(sb, &map_w, kb * 128, n0, &full_bar[s]);
+              } else {
+                const int ks = (kb - p.kb_int) * 64;
+                tma_load_2d(sa, &map_as, ks, m0, &full_bar[s]);
+                tma_load_2d(sb, &map_ws, ks, n0, &full_bar[s]);
+              }
             }
           }
         }
       }
-    } else if (warp == kMmaWarp) {
+    } else if (warp == kMmaWarp && leader) {
       // ------------------------------------------------------------------ MMA issuer
       // Whole warp, warp-uniform control flow, one elected lane issues.  Per K block the elected lane runs ONE asm
       // block (4 MMAs) plus the commits; descriptors are 32-bit low words advanced by constants.
-      constexpr uint32_t idesc_i8 = umma_idesc(2u, 1u, BM, BN);
-      const uint32_t idesc_f16 = umma_idesc(1u, Num<OutT>::kDtype == MQ_BF16 ? 1u : 0u, BM, BN);
+      constexpr uint32_t idesc_i8 = umma_idesc(2u, 1u, TM, BN);
+      const uint32_t idesc_f16 = umma_idesc(1u, Num<OutT>::kDtype == MQ_BF16 ? 1u : 0u, TM, BN);
+      // pair: the MMAs span both SMs and every completion is multicast to the same barrier of both CTAs
+      auto commit = [](uint32_t bar) {
+        if (kPair) tc_commit_pair(bar);
+        else tc_commit_a(bar);
+      };
 #ifdef MQ_DEBUG_NOMMA
       const bool issue = false;
 #else
@@ -256,7 +293,7 @@ mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
       const int upb = p.g >= 128 ? 1 : 128 / p.g;   // units per K block       (g  < 128)
       const int spu = p.g >= 128 ? 4 : p.g / 32;    // MMAs per unit inside one K block
       uint32_t kbc = 0, uc = 0;  // K blocks consumed, units issued (ring positions)
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      for (int tile = wid; tile < num_tiles; tile += wstride) {
         if (p.g >= 128) {
           for (int u = 0; u < p.G; ++u, ++uc) {
             const uint32_t t = uc & 1u;
@@ -270,11 +307,16 @@ mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
               tc_fence_after();
               const uint32_t sa = smem_a + s * (uint32_t)L::kStageBytes;
               if (elect_one()) {
-                if (issue)
-                  mma_i8_block4(tmem_base + t * BN, umma_desc_lo(sa), umma_desc_lo(sa + L::kABytes), idesc_i8,
-                                (kPreload || b > 0) ? 1u : 0u);
-                tc_commit_a(empty_a + s * 8u);                    // smem stage free once these MMAs have read it
-                if (b == bpu - 1) tc_commit_a(tfull_a + t * 8u);  // accumulator stage complete -> epilogue
+                if (issue) {
+                  if (kPair)
+                    mma_i8_block4_pair(tmem_base + t * BN, umma_desc_lo(sa), umma_desc_lo(sa + L::kABytes), idesc_i8,
+                                       (kPreload || b > 0) ? 1u : 0u);
+                  else
+                    mma_i8_block4(tmem_base + t * BN, umma_desc_lo(sa), umma_desc_lo(sa + L::kABytes), idesc_i8,
+                                  (kPreload || b > 0) ? 1u : 0u);
+                }
+                commit(empty_a + s * 8u);                    // smem stage free once these MMAs have read it
+                if (b == bpu - 1) commit(tfull_a + t * 8u);  // accumulator stage complete -> epilogue
               }
               __syncwarp();
             }
@@ -296,13 +338,16 @@ mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
               if (elect_one()) {
                 for (int sub = 0; sub < spu; ++sub) {
                   const uint32_t off = (uint32_t)((h * spu + sub) * 2);
-                  if (issue) mma_i8_lo(tmem_base + t * BN, la + off, lb + off, idesc_i8, (kPreload || sub > 0) ? 1u : 0u);
+                  if (issue) {
+                    if (kPair) mma_i8_lo_pair(tmem_base + t * BN, la + off, lb + off, idesc_i8, (kPreload || sub > 0) ? 1u : 0u);
+                    else mma_i8_lo(tmem_base + t * BN, la + off, lb + off, idesc_i8, (kPreload || sub > 0) ? 1u : 0u);
+                  }
                 }
-                tc_commit_a(tfull_a + t * 8u);
+                commit(tfull_a + t * 8u);
               }
               __syncwarp();
             }
-            if (elect_one()) tc_commit_a(empty_a + s * 8u);
+            if (elect_one()) commit(empty_a + s * 8u);
             __syncwarp();
           }
         }
@@ -318,11 +363,16 @@ mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
             tc_fence_after();
             const uint32_t sa = smem_a + s * (uint32_t)L::kStageBytes;
             if (elect_one()) {
-              if (issue)
-                mma_f16_block4(tmem_base + t * BN, umma_desc_lo(sa), umma_desc_lo(sa + L::kABytes), idesc_f16,
-                               kb > 0 ? 1u : 0u);
-              tc_commit_a(empty_a + s * 8u);
-              if (kb == p.kb_sal - 1) tc_commit_a(tfull_a + t * 8u);
+              if (issue) {
+                if (kPair)
+                  mma_f16_block4_pair(tmem_base + t * BN, umma_desc_lo(sa), umma_desc_lo(sa + L::kABytes), idesc_f16,
+                                      kb > 0 ? 1u : 0u);
+                else
+                  mma_f16_block4(tmem_base + t * BN, umma_desc_lo(sa), umma_desc_lo(sa + L::kABytes), idesc_f16,
+                                 kb > 0 ? 1u : 0u);
+              }
+              commit(empty_a + s * 8u);
+              if (kb == p.kb_sal - 1) commit(tfull_a + t * 8u);
             }
             __syncwarp();
           }
@@ -342,6 +392,12 @@ mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
     const uint32_t sas_a = smem_u32(sscale) + (uint32_t)(BN + row) * 4u;
     const uint32_t tfull_a = smem_u32(tfull_bar), tempty_a = smem_u32(tempty_bar);
     const uint32_t sfull_a = smem_u32(sfull_bar), sempty_a = smem_u32(sempty_bar);
+    // a drained accumulator stage is handed back to the MMA issuer: the leader CTA's barrier in a pair
+    const uint32_t tempty_l = kPair ? mapa_u32(tempty_a, 0u) : tempty_a;
+    auto release_tmem = [tempty_l](uint32_t t) {
+      if (kPair) mbar_arrive_cluster(tempty_l + t * 8u);
+      else mbar_arrive_a(tempty_l + t * 8u);
+    };
     const uint32_t tmem_lane = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)col0;
     uint32_t uc = 0, sc = 0;
     uint32_t magic[8];
@@ -355,12 +411,12 @@ mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
       tc_fence_before();
       __syncwarp();
       if (lane == 0) {
-        mbar_arrive_a(tempty_a);
-        mbar_arrive_a(tempty_a + 8u);
+        release_tmem(0u);
+        release_tmem(1u);
       }
     }
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-      const int m0 = (tile / p.tiles_n) * BM, n0 = (tile % p.tiles_n) * BN;
+    for (int tile = wid; tile < num_tiles; tile += wstride) {
+      const int m0 = (tile / p.tiles_n) * TM + (int)cta_rank * BM, n0 = (tile % p.tiles_n) * BN;
       const int m = m0 + row;
       const bool row_ok = m < p.M;
       float2 acc[CW / 2];
@@ -401,7 +457,7 @@ mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
             if (kPreload) tmem_st_wait();
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive_a(tempty_a + t * 8u);
+            if (lane == 0) release_tmem(t);
           }
           const uint32_t* vv = v[c & 1];
 #ifdef MQ_DEBUG_NOMATH
@@ -460,7 +516,7 @@ mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
             if (kPreload) tmem_st_wait();
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive_a(tempty_a + t * 8u);
+            if (lane == 0) release_tmem(t);
           }
           const uint32_t* vv = v[c & 1];
 #pragma unroll
@@ -552,10 +608,12 @@ teardown:
     }
   }
   tc_fence_before();
-  __syncthreads();
+  if (kPair) cluster_sync_all();  // no CTA leaves while its peer may still signal its barriers or read its operands
+  else __syncthreads();
   if (warp == kAllocWarp) {
     tc_fence_after();
-    tmem_dealloc<kTmemCols>(tmem_base);
+    if (kPair) tmem_dealloc_pair<kTmemCols>(tmem_base);
+    else tmem_dealloc<kTmemCols>(tmem_base);
   }
 }
 
@@ -601,27 +659,48 @@ int make_map(CUtensorMap* map, const void* ptr, CUtensorMapDataType dt, int esiz
   return MQ_OK;
 }
 
-template <typename OutT, int BN, int kStages>
+template <typename OutT, int BN, int kStages, bool kPair = false>
 int launch_gemm(const CUtensorMap& ma, const CUtensorMap& mw, const CUtensorMap& mas, const CUtensorMap& mws,
                 const CUtensorMap& msa, const CUtensorMap& msw, GemmArgs p, cudaStream_t st) {
-  using L = SmemLayout<BN, kStages>;
+  using L = SmemLayout<BN, kStages, kPair>;
   p.debug = mq_get_option("gemm_debug", 0);
   p.profile = mq_get_option("gemm_profile", 0);
-  auto kern = p.profile ? mixed_gemm_kernel<OutT, BN, kStages, true> : mixed_gemm_kernel<OutT, BN, kStages, false>;
+  auto kern = p.profile ? mixed_gemm_kernel<OutT, BN, kStages, true, kPair>
+                        : mixed_gemm_kernel<OutT, BN, kStages, false, kPair>;
   MQ_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal));
-  p.tiles_m = (p.M + BM - 1) / BM;
+  constexpr int TM = kPair ? 2 * BM : BM;
+  p.tiles_m = (p.M + TM - 1) / TM;
   p.tiles_n = (p.N + BN - 1) / BN;
   const int64_t tiles = (int64_t)p.tiles_m * p.tiles_n;
-  int64_t grid = mq_get_option("gemm_persistent", 0) == 2 ? tiles : (int64_t)mq_sm_count();
+  const int64_t workers = kPair ? (int64_t)mq_sm_count() / 2 : (int64_t)mq_sm_count();
+  int64_t grid = mq_get_option("gemm_persistent", 0) == 2 ? tiles : workers;
   if (grid > tiles) grid = tiles;
-  kern<<<(unsigned)grid, kThreads, L::kTotal, st>>>(ma, mw, mas, mws, msa, msw, p);
+  if (!kPair) {
+    kern<<<(unsigned)grid, kThreads, L::kTotal, st>>>(ma, mw, mas, mws, msa, msw, p);
+  } else {  // one cluster of two CTAs (the two SMs of a TPC) per worker
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((unsigned)(2 * grid));
+    cfg.blockDim = dim3(kThreads);
+    cfg.dynamicSmemBytes = L::kTotal;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    MQ_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kern, ma, mw, mas, mws, msa, msw, p));
+  }
   MQ_CHECK_CUDA(cudaGetLastError());
   return MQ_OK;
 }
 
 template <typename OutT>
 int dispatch_gemm(const CUtensorMap& ma, const CUtensorMap& mw, const CUtensorMap& mas, const CUtensorMap& mws,
-                  const CUtensorMap& msa, const CUtensorMap& msw, const GemmArgs& p, int bn, cudaStream_t st) {
+                  const CUtensorMap& msa, const CUtensorMap& msw, const GemmArgs& p, int bn, bool pair,
+                  cudaStream_t st) {
+  if (bn == 256 && pair) return launch_gemm<OutT, 256, 6, true>(ma, mw, mas, mws, msa, msw, p, st);
   if (bn == 256) return launch_gemm<OutT, 256, 4>(ma, mw, mas, mws, msa, msw, p, st);
   return launch_gemm<OutT, 128, 6>(ma, mw, mas, mws, msa, msw, p, st);
 }
@@ -672,12 +751,15 @@ int mq_mixed_gemm(const int8_t* a_codes, int64_t lda, const float* a_scales, int
   }
   int bn = mq_get_option("gemm_bn", 0);
   if (bn != 128 && bn != 256) bn = N >= 256 ? 256 : 128;
+  // CTA pairs (256 x 256 tiles over two SMs, each staging half of the W tile): option gemm_pair = 1 on, 2 off
+  const bool pair = bn == 256 && M > BM && mq_get_option("gemm_pair", MQ_GEMM_PAIR_DEFAULT) == 1;
+  const int wbox = pair ? bn / 2 : bn;  // W rows per TMA box
 
   CUtensorMap ma, mw, mas, mws, msa, msw;
   int rc;
   if (G > 0) {
     if ((rc = make_map(&ma, a_codes, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, M, kc, lda, BM))) return rc;
-    if ((rc = make_map(&mw, w_codes, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, N, kc, ldw, bn))) return rc;
+    if ((rc = make_map(&mw, w_codes, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, N, kc, ldw, wbox))) return rc;
     // scale vectors: [G, M] / [G, N] fp32, one row of BM / BN values per unit (rows and columns past M / N read 0)
     if ((rc = make_map(&msa, a_scales, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, G, M, ld_as, 1, BM))) return rc;
     if ((rc = make_map(&msw, w_scales, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, G, N, ld_ws, 1, bn))) return rc;
@@ -685,7 +767,7 @@ int mq_mixed_gemm(const int8_t* a_codes, int64_t lda, const float* a_scales, int
   const CUtensorMapDataType dt16 = dtype == MQ_F16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
   if (Ks > 0) {  // the tensor maps cover exactly Ks columns: TMA zero-fills the tail of the last 64-column block
     if ((rc = make_map(&mas, a_sal, dt16, 2, M, Ks, ld_asal, BM))) return rc;
-    if ((rc = make_map(&mws, w_sal, dt16, 2, N, Ks, ld_wsal, bn))) return rc;
+    if ((rc = make_map(&mws, w_sal, dt16, 2, N, Ks, ld_wsal, wbox))) return rc;
   } else {
     mas = ma;
     mws = mw;
@@ -701,8 +783,8 @@ int mq_mixed_gemm(const int8_t* a_codes, int64_t lda, const float* a_scales, int
   p.y = y; p.ldy = ldy; p.M = (int)M; p.N = (int)N; p.G = (int)G; p.g = G > 0 ? group_size : 32;
   p.kb_int = (int)(kc / 128); p.kb_sal = (int)((Ks + 63) / 64);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  if (dtype == MQ_F16) return dispatch_gemm<__half>(ma, mw, mas, mws, msa, msw, p, bn, st);
-  return dispatch_gemm<__nv_bfloat16>(ma, mw, mas, mws, msa, msw, p, bn, st);
+  if (dtype == MQ_F16) return dispatch_gemm<__half>(ma, mw, mas, mws, msa, msw, p, bn, pair, st);
+  return dispatch_gemm<__nv_bfloat16>(ma, mw, mas, mws, msa, msw, p, bn, pair, st);
 }
 
 // debug: per-CTA wait-cycle profile of the last mixed GEMM launched with option gemm_profile != 0 (see kProfSlots).

@@ -278,7 +278,7 @@ __host__ __device__ constexpr uint32_t umma_idesc(uint32_t d_fmt, uint32_t ab_fm
 // advance by 32 B >> 4 = 2 per slice; the high word -- SBO 1024 B, version 1, SWIZZLE_128B -- is constant), so that
 // the issuing thread spends a handful of instructions per K block instead of a descriptor rebuild per MMA.
 constexpr uint32_t kDescHiK128 = 0x40004040u;  // == umma_desc_k128(x) >> 32
-#define MQ_MMA_BLOCK4(NAME, KIND)                                                                                   \
+#define MQ_MMA_BLOCK4(NAME, KIND, GRP)                                                                                 \
   __device__ __forceinline__ void NAME(uint32_t tmem_d, uint32_t lo_a, uint32_t lo_b, uint32_t idesc,              \
                                        uint32_t acc_first) {                                                        \
     asm volatile(                                                                                                   \
@@ -286,18 +286,21 @@ constexpr uint32_t kDescHiK128 = 0x40004040u;  // == umma_desc_k128(x) >> 32
         "setp.ne.b32 p, %4, 0;\n\t"                                                                                 \
         "setp.eq.b32 q, 0, 0;\n\t"                                                                                  \
         "mov.b64 da, {%1, %5};\n\tmov.b64 db, {%2, %5};\n\t"                                                        \
-        "tcgen05.mma.cta_group::1.kind::" KIND " [%0], da, db, %3, p;\n\t"                                          \
+        "tcgen05.mma.cta_group::" GRP ".kind::" KIND " [%0], da, db, %3, p;\n\t"                                        \
         "add.u32 la, %1, 2;\n\tadd.u32 lb, %2, 2;\n\tmov.b64 da, {la, %5};\n\tmov.b64 db, {lb, %5};\n\t"            \
-        "tcgen05.mma.cta_group::1.kind::" KIND " [%0], da, db, %3, q;\n\t"                                          \
+        "tcgen05.mma.cta_group::" GRP ".kind::" KIND " [%0], da, db, %3, q;\n\t"                                        \
         "add.u32 la, %1, 4;\n\tadd.u32 lb, %2, 4;\n\tmov.b64 da, {la, %5};\n\tmov.b64 db, {lb, %5};\n\t"            \
-        "tcgen05.mma.cta_group::1.kind::" KIND " [%0], da, db, %3, q;\n\t"                                          \
+        "tcgen05.mma.cta_group::" GRP ".kind::" KIND " [%0], da, db, %3, q;\n\t"                                        \
         "add.u32 la, %1, 6;\n\tadd.u32 lb, %2, 6;\n\tmov.b64 da, {la, %5};\n\tmov.b64 db, {lb, %5};\n\t"            \
-        "tcgen05.mma.cta_group::1.kind::" KIND " [%0], da, db, %3, q;\n\t}" ::"r"(tmem_d),                          \
+        "tcgen05.mma.cta_group::" GRP ".kind::" KIND " [%0], da, db, %3, q;\n\t}" ::"r"(tmem_d),                        \
         "r"(lo_a), "r"(lo_b), "r"(idesc), "r"(acc_first), "r"(kDescHiK128)                                          \
         : "memory");                                                                                                \
   }
-MQ_MMA_BLOCK4(mma_i8_block4, "i8")
-MQ_MMA_BLOCK4(mma_f16_block4, "f16")
+MQ_MMA_BLOCK4(mma_i8_block4, "i8", "1")
+MQ_MMA_BLOCK4(mma_f16_block4, "f16", "1")
+// CTA-pair forms (M = 256 over two SMs; issued by the leader CTA only)
+MQ_MMA_BLOCK4(mma_i8_block4_pair, "i8", "2")
+MQ_MMA_BLOCK4(mma_f16_block4_pair, "f16", "2")
 #undef MQ_MMA_BLOCK4
 // low word of the K-major SWIZZLE_128B descriptor of the tile at shared address `smem_addr`
 __device__ __forceinline__ uint32_t umma_desc_lo(uint32_t smem_addr) {
@@ -315,6 +318,67 @@ __device__ __forceinline__ void mma_i8_lo(uint32_t tmem_d, uint32_t lo_a, uint32
 }
 __device__ __forceinline__ void tc_commit_a(uint32_t bar_addr) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar_addr) : "memory");
+}
+
+// ------------------------------------------------------------------------------------------------ CTA pairs
+// cta_group::2: two CTAs of one cluster (the two SMs of a TPC) run one M = 256 MMA; each CTA stages its own 128 rows
+// of A and HALF of the B tile, owns the 128 accumulator lanes of its rows, and only the leader (rank 0) issues.
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {  // every thread of both CTAs
+  __syncwarp();
+  asm volatile("barrier.cluster.arrive.release;\n\tbarrier.cluster.wait.acquire;" ::: "memory");
+}
+// shared::cluster address of the same shared-memory offset in CTA `rank` of the cluster
+__device__ __forceinline__ uint32_t mapa_u32(uint32_t cta_addr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(cta_addr), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+// tile into THIS CTA's shared memory, completion bytes onto an mbarrier given by its shared::cluster address (the
+// leader's full barrier)
+__device__ __forceinline__ void tma_load_2d_pair(void* dst_smem, const CUtensorMap* map, int32_t c0, int32_t c1,
+                                                 uint32_t bar_cluster_addr) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], "
+      "[%2];" ::"r"(smem_u32(dst_smem)),
+      "l"(map), "r"(bar_cluster_addr), "r"(c0), "r"(c1)
+      : "memory");
+}
+template <int kCols>
+__device__ __forceinline__ void tmem_alloc_pair(uint32_t* dst_smem) {  // the same warp of BOTH CTAs
+  asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(dst_smem)),
+               "n"(kCols)
+               : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+template <int kCols>
+__device__ __forceinline__ void tmem_dealloc_pair(uint32_t taddr) {
+  asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "n"(kCols) : "memory");
+}
+// arrive on the mbarrier at this shared-memory offset in BOTH CTAs once the pair's MMAs issued so far have completed
+__device__ __forceinline__ void tc_commit_pair(uint32_t bar_addr) {
+  asm volatile(
+      "{\n\t.reg .b16 m;\n\tmov.b16 m, 3;\n\t"
+      "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], m;\n\t}" ::"r"(
+          bar_addr)
+      : "memory");
+}
+__device__ __forceinline__ void mma_i8_lo_pair(uint32_t tmem_d, uint32_t lo_a, uint32_t lo_b, uint32_t idesc,
+                                               uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "mov.b64 da, {%1, %5};\n\tmov.b64 db, {%2, %5};\n\t"
+      "tcgen05.mma.cta_group::2.kind::i8 [%0], da, db, %3, p;\n\t}" ::"r"(tmem_d),
+      "r"(lo_a), "r"(lo_b), "r"(idesc), "r"(accumulate), "r"(kDescHiK128)
+      : "memory");
 }
 
 }  // namespace mqptx

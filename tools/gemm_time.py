@@ -24,6 +24,8 @@ gi = max(0, min(G, int(round(G * frac)) // step * step))
 a = ops.quant_rows(x, perm, sal, g, int_groups=gi)
 wq = ops.quant_rows(w, perm, sal, g, int_groups=gi)
 _lib.set_option("gemm_debug", debug)
+if os.environ.get("MQ_PAIR"):
+    _lib.set_option("gemm_pair", int(os.environ["MQ_PAIR"]))      # 1: CTA-pair kernel, 2: single-CTA kernel
 if debug:
     _lib.set_option("gemm_profile", 1)      # the debug bits live in the profiling variant of the kernel
 for _ in range(3):
@@ -46,5 +48,5 @@ if os.environ.get("MQ_PROFILE"):
     med["clock_ghz"] = med["cycles"] / max(med["ns"], 1)
     print("PROF " + json.dumps(med), flush=True)
     _lib.set_option("gemm_profile", 0)
-print("GEMM " + json.dumps(dict(M=M, N=N, K=K, g=g, p=p, int_groups=gi, groups=G, debug=debug, ms=ms, tops=2.0 * M * N * K / ms / 1e9,
+print("GEMM " + json.dumps(dict(M=M, N=N, K=K, g=g, p=p, int_groups=gi, groups=G, pair=os.environ.get('MQ_PAIR', ''), debug=debug, ms=ms, tops=2.0 * M * N * K / ms / 1e9,
                                 fault=_lib.gemm_fault()[:5])), flush=True)
