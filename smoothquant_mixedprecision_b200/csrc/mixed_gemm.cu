@@ -74,7 +74,7 @@ struct GemmArgs {
 #endif
 constexpr bool kPreload = MQ_GEMM_PRELOAD != 0;
 #ifndef MQ_GEMM_PAIR_DEFAULT
-#define MQ_GEMM_PAIR_DEFAULT 2  // 1: CTA-pair kernel whenever BN = 256 and M > 128;  2: single-CTA kernel
+#define MQ_GEMM_PAIR_DEFAULT 3  // 1: CTA-pair kernel whenever possible;  2: single-CTA kernel;  3: by tile count
 #endif
 constexpr int kScaleSlots = 8;  // ring of per-unit scale vectors (ws[BN] | as[BM], fp32) staged in shared memory by TMA
 
@@ -751,8 +751,12 @@ int mq_mixed_gemm(const int8_t* a_codes, int64_t lda, const float* a_scales, int
   }
   int bn = mq_get_option("gemm_bn", 0);
   if (bn != 128 && bn != 256) bn = N >= 256 ? 256 : 128;
-  // CTA pairs (256 x 256 tiles over two SMs, each staging half of the W tile): option gemm_pair = 1 on, 2 off
-  const bool pair = bn == 256 && M > BM && mq_get_option("gemm_pair", MQ_GEMM_PAIR_DEFAULT) == 1;
+  // CTA pairs (256 x 256 tiles over two SMs, each staging half of the W tile).  Option gemm_pair: 1 always (when
+  // BN = 256 and M > 128), 2 never; default: whenever the pairs still get at least two tiles each -- below that the
+  // single-CTA kernel spreads the few tiles over twice as many workers (2048 x 4096: 0.066 vs 0.067 ms).
+  const int pair_opt = mq_get_option("gemm_pair", MQ_GEMM_PAIR_DEFAULT);
+  const int64_t pair_tiles = ((M + 2 * BM - 1) / (2 * BM)) * ((N + 255) / 256);
+  const bool pair = bn == 256 && M > BM && (pair_opt == 1 || (pair_opt == 3 && pair_tiles >= (int64_t)mq_sm_count()));
   const int wbox = pair ? bn / 2 : bn;  // W rows per TMA box
 
   CUtensorMap ma, mw, mas, mws, msa, msw;

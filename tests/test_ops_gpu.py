@@ -359,3 +359,35 @@ def test_hybrid_split_tail_is_the_reference_dequantised_value(ops, mqlib, g, Gi,
     tol = (2e-3 if dtype == torch.float16 else 1.6e-2) * float(ref.abs().max()) + 1e-3
     assert err <= tol, (err, tol)
     assert mqlib.gemm_fault()[0] == 0 and mqlib.quant_fault()[0] == 0
+
+
+@pytest.mark.parametrize("M,N,K,g,p,frac", [(256, 256, 512, 128, 0.0, 1.0), (1000, 1000, 2048, 128, 0.05, 1.0),
+                                            (300, 512, 1024, 64, 0.05, 1.0), (777, 768, 1024, 32, 0.1, 1.0),
+                                            (2048, 512, 4096, 1024, 0.05, 1.0), (1500, 1280, 2048, 128, 0.05, 0.5),
+                                            (640, 256, 1024, 128, 0.05, 0.0)])
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+def test_cta_pair_kernel_is_bit_identical_to_single_cta_kernel(ops, mqlib, M, N, K, g, p, frac, dtype):
+    """The cta_group::2 kernel (256 x 256 tiles over two SMs) issues the same MMAs and accumulates every output
+    element in the same order as the single-CTA kernel: outputs must be equal bit for bit, ragged edges included."""
+    x = synth(M, K, dtype, 5).to(DEV)
+    w = (torch.randn(N, K, generator=torch.Generator().manual_seed(6)) * 0.05).to(dtype).to(DEV)
+    order = torch.randperm(K, generator=torch.Generator().manual_seed(7))
+    ks = int(p * K)
+    perm = order[ks:].int().to(DEV)
+    sal = torch.sort(order[:ks]).values.int().to(DEV) if ks else None
+    G = (K - ks + g - 1) // g
+    step = max(1, 128 // g)
+    gi = int(round(G * frac)) // step * step
+    a = ops.quant_rows(x, perm, sal, g, int_groups=gi)
+    wq = ops.quant_rows(w, perm, sal, g, int_groups=gi)
+    bias = torch.randn(N, generator=torch.Generator().manual_seed(8)).to(dtype).to(DEV)
+    try:
+        mqlib.set_option("gemm_pair", 2)
+        y0 = ops.mixed_gemm(a, wq, bias)
+        mqlib.set_option("gemm_pair", 1)
+        y1 = ops.mixed_gemm(a, wq, bias)
+    finally:
+        mqlib.set_option("gemm_pair", 0)
+    torch.cuda.synchronize()
+    assert mqlib.gemm_fault()[0] == 0
+    assert torch.equal(y0, y1)
