@@ -284,6 +284,13 @@ def gpu_arm(args):
     bf16 = peaks.get("bf16_tflops_sustained") or 1400.0          # fallback: B200_PROFILING.md sustained figure
     peak_src = "measured (MEASURED_PEAKS.json bf16_tflops_sustained; int8 taken as 2x)" if peaks else \
         "fallback 1.4 PF bf16 sustained; int8 taken as 2x"
+    traffic = {}                                                  # per-launch DRAM bytes from the committed ncu pass
+    try:
+        import glob
+        tfile = sorted(glob.glob(os.path.join(ROOT, "profiles", "*_traffic.json")))[-1]
+        traffic = {k: v["dram_bytes_per_launch"] for k, v in json.load(open(tfile))["kernels"].items()}
+    except (IndexError, OSError, KeyError, ValueError):
+        pass
     t_roof_ms = (ops_i8 / (2 * bf16 * 1e12) + ops_f16 / (bf16 * 1e12)) * 1e3
     achieved = (ops_i8 + ops_f16) / (gemm_ms * 1e-3) / 1e12
     peak_mix = (ops_i8 + ops_f16) / (t_roof_ms * 1e-3) / 1e12
@@ -302,13 +309,16 @@ def gpu_arm(args):
                     "d2h_bytes_per_step": hy.numel() * 2, "ms_per_step": ms_e2e},
             "gpu_launches": launches,
             "roofline": {"kernel": "mixed_gemm_kernel", "bound": "tensor", "achieved": achieved, "peak": peak_mix,
-                         "unit": "TOP/s", "frac": achieved / peak_mix, "traffic": None, "peak_source": peak_src,
+                         "unit": "TOP/s", "frac": achieved / peak_mix, "traffic": traffic.get("mixed_gemm_kernel"),
+                         "traffic_unit": "DRAM bytes per launch (ncu, profiles/*_traffic.json)", "peak_source": peak_src,
                          "share_of_step": gemm_ms / ms, "launches_per_step": len(ev) // args.steps},
             "roofline_quantiser": {"kernel": "quant_rows_fast", "bound": "hbm",
                                    "achieved": quant_bytes / (quant_ms * 1e-3) / 1e9,
                                    "peak": peaks.get("hbm_gbs") or 6500.0, "unit": "GB/s",
                                    "frac": quant_bytes / (quant_ms * 1e-3) / 1e9 / (peaks.get("hbm_gbs") or 6500.0),
-                                   "traffic": None, "share_of_step": quant_ms / ms,
+                                   "traffic": traffic.get("quant_rows_fast"),
+                                   "algorithmic_bytes_per_launch": quant_bytes / max(1, len(qev) // args.steps),
+                                   "share_of_step": quant_ms / ms,
                                    "launches_per_step": len(qev) // args.steps},
             "clocks": clocks}
     if world == 1 and not args.no_cpu_baseline:

@@ -36,6 +36,7 @@ __all__ = [
     "quantize_activation_per_token_absmax", "quantize_activation_per_tensor_absmax",
     "quantize_activation_per_group_absmax", "quantize_activation_per_group_absmax_sort",
     "quantize_weight_per_group_absmax_sort", "W4A4Linear", "quantize_opt", "quantize_llama_like", "quantize_model",
+    "save_packed_model", "load_packed_model",
 ]
 
 SORT_KINDS = ("max", "mean3std", "argmax", "none")
@@ -158,6 +159,9 @@ def _shared_act(xin, mod):
 def _check_choice(value, allowed, what):
     if value not in allowed:
         raise ValueError(f"Invalid {what}: {value}")
+
+
+PACKED_FORMAT = 1      # version tag of packed_state / save_packed_model
 
 
 class W4A4Linear(nn.Module):
@@ -402,10 +406,7 @@ class W4A4Linear(nn.Module):
                             int_groups=self.int_groups)
         self.perm = perm
         self.w_codes, self.w_scales, self.w_sal = wq.codes, wq.scales, wq.sal
-        import hashlib
-        h = hashlib.sha1(perm.cpu().numpy().tobytes())
-        h.update(b"|" if sal is None else sal.cpu().numpy().tobytes())
-        self._partition_id = (h.hexdigest(), self.group_size, self.quant_bits, self.int_groups)
+        self._set_partition_id()
 
     @torch.no_grad()
     def dequantized_weight(self):
@@ -444,6 +445,69 @@ class W4A4Linear(nn.Module):
         if self.bias is not None:
             n += self.bias.numel() * self.bias.element_size()
         return n
+
+    # ---- packed checkpoint.  The reference never serialises its W4A4 layers (it re-quantises on
+    # every run, 54 s for OPT-1.3B); the INT8 analogue is examples/export_int8_model.py:45-56.
+    @torch.no_grad()
+    def packed_state(self) -> Dict[str, object]:
+        """Everything needed to rebuild this layer without the float weight: int4 nibbles (mq_pack_int4) + group
+        scales in the 16-bit compute dtype + 16-bit salient slice + permutation (fused mode), or the literal
+        fake-quantised weight (reference mode).  Tensors are returned on the CPU."""
+        if self.tp_world != 1:
+            raise RuntimeError("save the unsharded layer and shard after loading (shard_ slices packed rows)")
+        cpu = lambda t: None if t is None else t.detach().cpu()
+        meta = dict(format=PACKED_FORMAT, in_features=self.in_features, out_features=self.out_features,
+                    group_size=self.group_size, quant_bits=self.quant_bits, mode=self.mode, sort=self.sort,
+                    act_quant=self.act_quant_name, weight_quant=self.weight_quant_name,
+                    output_quant=self.output_quant_name, int_groups=self.int_groups, int_fraction=self.int_fraction)
+        st = {"meta": meta, "bias": cpu(self.bias), "salient_indices": cpu(self.salient_indices)}
+        if self.mode == "fused" and self.w_codes is not None:
+            sdt = self.w_sal.dtype if self.w_sal is not None else torch.float32
+            sc16 = self.w_scales.to(sdt)
+            if not torch.equal(sc16.float(), self.w_scales):        # scales are values of the compute dtype (DESIGN 2)
+                sc16 = self.w_scales
+            st.update(w_packed=cpu(ops.pack_int4(self.w_codes)), w_scales=cpu(sc16), w_sal=cpu(self.w_sal),
+                      perm=cpu(self.perm))
+        else:
+            st["weight"] = cpu(self._weight)
+        return st
+
+    @staticmethod
+    @torch.no_grad()
+    def from_packed(state, device="cuda"):
+        """Inverse of :meth:`packed_state`: no quantisation work, only mq_unpack_int4 of the nibbles."""
+        meta = state["meta"]
+        if meta.get("format") != PACKED_FORMAT:
+            raise ValueError(f"unknown packed W4A4 format: {meta.get('format')}")
+        dev = torch.device(device)
+        if dev.type != "cuda":
+            raise RuntimeError("W4A4Linear.from_packed needs a CUDA device (no CPU fallback)")
+        new = W4A4Linear(meta["in_features"], meta["out_features"], state["bias"] is not None,
+                         act_quant=meta["act_quant"], quantize_output=meta["output_quant"] != "None",
+                         quant_bits=meta["quant_bits"], group_size=meta["group_size"], mode=meta["mode"],
+                         sort=meta["sort"], device="meta")
+        new.weight_quant_name = meta["weight_quant"]
+        new.salient_indices = state["salient_indices"]
+        new.int_groups, new.int_fraction = meta["int_groups"], meta["int_fraction"]
+        put = lambda t: None if t is None else t.to(dev)
+        new._buffers["bias"] = put(state["bias"])
+        new._buffers["_weight"] = None
+        if "w_packed" in state:
+            new.w_codes = ops.unpack_int4(put(state["w_packed"]).contiguous())
+            new.w_scales = put(state["w_scales"]).float().contiguous()
+            new.w_sal, new.perm = put(state["w_sal"]), put(state["perm"])
+            new._set_partition_id()
+        else:
+            new._buffers["_weight"] = put(state["weight"])
+        new._device_indices(dev)
+        return new
+
+    def _set_partition_id(self):
+        import hashlib
+        sal, _ = self._device_indices(self.perm.device)
+        h = hashlib.sha1(self.perm.cpu().numpy().tobytes())
+        h.update(b"|" if sal is None else sal.cpu().numpy().tobytes())
+        self._partition_id = (h.hexdigest(), self.group_size, self.quant_bits, self.int_groups)
 
     def __repr__(self):
         return (f"W4A4Linear({self.in_features}, {self.out_features}, bias={self.bias is not None}, "
@@ -531,3 +595,43 @@ def model_packed_bytes(model) -> Dict[str, int]:
     lin = sum(m.packed_bytes() for m in model.modules() if isinstance(m, W4A4Linear))
     other = sum(p.numel() * p.element_size() for p in model.parameters())
     return {"w4a4_linear_bytes": lin, "other_parameter_bytes": other, "total_bytes": lin + other}
+
+
+# ------------------------------------------------------------------------------------------- packed checkpoints
+def save_packed_model(model, path=None) -> Dict[str, object]:
+    """Checkpoint of a quantised model: the packed state of every W4A4Linear (by module name) plus the ordinary
+    state_dict entries of everything else.  Written with torch.save when ``path`` is given; returned either way."""
+    linears = {n: m.packed_state() for n, m in model.named_modules() if isinstance(m, W4A4Linear)}
+    rest = {k: v.detach().cpu() for k, v in model.state_dict().items()
+            if not any(k == n or k.startswith(n + ".") for n in linears)}
+    ckpt = {"format": PACKED_FORMAT, "linears": linears, "rest": rest}
+    if path is not None:
+        torch.save(ckpt, path)
+    return ckpt
+
+
+def load_packed_model(model, ckpt, device="cuda"):
+    """Turn a float skeleton of the same architecture (any weights, any real device) into the quantised
+    model of the checkpoint: every named linear becomes ``W4A4Linear.from_packed`` (no re-quantisation), every other
+    tensor is loaded from the checkpoint.  ``ckpt`` is a path or the dict returned by save_packed_model."""
+    if not isinstance(ckpt, dict):
+        ckpt = torch.load(ckpt, map_location="cpu", weights_only=False)
+    if ckpt.get("format") != PACKED_FORMAT:
+        raise ValueError(f"unknown packed checkpoint format: {ckpt.get('format')}")
+    if any(p.is_meta for p in model.parameters()):
+        raise ValueError("load_packed_model needs a materialised skeleton: non-persistent buffers (rotary tables) are "
+                         "not part of any checkpoint and would stay uninitialised on a meta skeleton")
+    model.to(device)
+    for name, st in ckpt["linears"].items():
+        parent_name, _, attr = name.rpartition(".")
+        parent = model.get_submodule(parent_name) if parent_name else model
+        old = getattr(parent, attr)                                  # KeyError / AttributeError on a foreign skeleton
+        if not isinstance(old, (nn.Linear, W4A4Linear)):
+            raise TypeError(f"{name} is a {type(old).__name__}, not a linear layer")
+        setattr(parent, attr, W4A4Linear.from_packed(st, device))
+    own = {k for n in ckpt["linears"] for k in model.state_dict() if k == n or k.startswith(n + ".")}
+    missing, unexpected = model.load_state_dict(ckpt["rest"], strict=False)
+    missing = [k for k in missing if k not in own]
+    if missing or unexpected:
+        raise KeyError(f"packed checkpoint does not match the skeleton: missing {missing}, unexpected {unexpected}")
+    return model

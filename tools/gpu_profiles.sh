@@ -18,6 +18,10 @@ $BCMD > gpurun_out/bench_l2.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -k regex:"mixed_gemm|quant_rows|colstat|argsort" -c 400 --csv \
     --log-file gpurun_out/${TAG}_launches.csv $BCMD > gpurun_out/ncu_launches.log 2>&1
 echo "launch list rc=$? lines=$(wc -l < gpurun_out/${TAG}_launches.csv)"
+# DRAM bytes per launch of the same command (roofline.traffic): one step of 2 layers = 2 x (7 GEMM + 4 quantiser)
+ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum --clock-control none -k regex:"mixed_gemm|quant_rows" -c 400 --csv \
+    --log-file gpurun_out/${TAG}_traffic.csv $BCMD > gpurun_out/ncu_traffic.log 2>&1
+python tools/traffic_summary.py gpurun_out/${TAG}_traffic.csv 22 gpurun_out/${TAG}_traffic.json
 # full captures: one GEMM launch and one quantiser launch at the 7B prefill shape
 GCMD="python tools/gemm_time.py 32768 4096 4096 128 0.05 2 0"
 $GCMD > gpurun_out/plain.log 2>&1 &&
