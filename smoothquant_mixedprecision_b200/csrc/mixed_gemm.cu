@@ -73,6 +73,26 @@ struct GemmArgs {
 #define MQ_GEMM_PRELOAD 1
 #endif
 constexpr bool kPreload = MQ_GEMM_PRELOAD != 0;
+// kMagicMma: the magic-number pattern is not stored by the epilogue threads (16 STTM + ~67 constant re-materialising
+// moves per unit and warp) but produced by the tensor core: before the integer MMAs of a unit the issuer runs ONE
+// kind::f16 MMA (K = 16, accumulate off) whose two operands are the same constant shared-memory atom -- every 16-byte
+// chunk holds six 1024.0 and two 0.0 halves, so every accumulator becomes 12 * 2^20 = 1.5 * 2^23 exactly (fp32), i.e.
+// the bit pattern 0x4B400000 the integer MMAs then accumulate onto.  Costs a quarter of a unit's tensor time at
+// g = 128 and removes a fifth of the epilogue's instructions.
+#ifndef MQ_GEMM_MAGIC_MMA
+#define MQ_GEMM_MAGIC_MMA 1
+#endif
+constexpr bool kMagicMma = MQ_GEMM_MAGIC_MMA != 0;
+constexpr bool kRefill = kPreload && !kMagicMma;       // the epilogue stores the pattern itself
+constexpr bool kBiased = kPreload || kMagicMma;        // drained words are the floats kMagic + sum
+#ifndef MQ_GEMM_UNIFORM
+#define MQ_GEMM_UNIFORM 2   // 0: plain thread-derived addresses (experiments), 1: uniform warp index, 2: + opaque uniform addresses
+#endif
+#ifndef MQ_GEMM_CH
+#define MQ_GEMM_CH 16
+#endif
+__device__ __forceinline__ void tmem_ld_chunk(uint32_t taddr, uint32_t (&v)[16]) { tmem_ld_32x16(taddr, v); }
+__device__ __forceinline__ void tmem_ld_chunk(uint32_t taddr, uint32_t (&v)[32]) { tmem_ld_32x32(taddr, v); }
 #ifndef MQ_GEMM_PAIR_DEFAULT
 #define MQ_GEMM_PAIR_DEFAULT 3  // 1: CTA-pair kernel whenever possible;  2: single-CTA kernel;  3: by tile count
 #endif
@@ -96,7 +116,8 @@ struct SmemLayout {
   static constexpr int kStageBytes = kABytes + kBBytes;
   // per scale slot: ws[BN] | as[BM]   (fp32)
   static constexpr int kSlotFloats = BN + BM;
-  static constexpr int kScaleOffset = kStages * kStageBytes;
+  static constexpr int kConstOffset = kStages * kStageBytes;  // 1024-byte constant atom (kMagicMma), 1024-aligned
+  static constexpr int kScaleOffset = kConstOffset + (kMagicMma ? 1024 : 0);
   static constexpr int kBarOffset = kScaleOffset + kScaleSlots * kSlotFloats * 4;
   // full[kStages], empty[kStages], tmem_full[2], tmem_empty[2], sfull[kScaleSlots], sempty[kScaleSlots], tmem base
   static constexpr int kBarBytes = (2 * kStages + 4 + 2 * kScaleSlots) * 8 + 16;
@@ -168,7 +189,13 @@ mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
   uint64_t* sempty_bar = sfull_bar + kScaleSlots;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(sempty_bar + kScaleSlots);
 
+#if MQ_GEMM_UNIFORM
+  // warp index through a lane-0 shuffle: ptxas then knows the value (and every TMEM / barrier address derived from
+  // it) is warp-uniform and keeps it in uniform registers instead of one R2UR per tcgen05 instruction
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
+#else
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+#endif
   const bool prof = kProf && p.profile != 0 && blockIdx.x < kProfCtas;
   const long long k_t0 = kProf ? clock64() : 0;
   const unsigned long long k_ns0 = kProf ? globaltimer_ns() : 0ull;
@@ -199,6 +226,13 @@ mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
     }
     fence_mbar_init();
   }
+  if (kMagicMma && warp == kAllocWarp + 1) {  // constant atom: per 16-byte chunk six halves of 1024.0 and two of 0.0
+    const uint4 chunk = make_uint4(0x64006400u, 0x64006400u, 0x64006400u, 0u);
+    uint4* atom = reinterpret_cast<uint4*>(smem + L::kConstOffset);
+    atom[lane] = chunk;
+    atom[lane + 32] = chunk;
+    fence_proxy_async_smem();  // generic-proxy stores -> visible to the tensor core's async-proxy reads
+  }
   if (warp == kAllocWarp) {
     if (kPair) tmem_alloc_pair<kTmemCols>(tmem_slot);
     else tmem_alloc<kTmemCols>(tmem_slot);
@@ -207,7 +241,11 @@ mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
   if (kPair) cluster_sync_all();  // barriers of both CTAs initialised before any remote arrive / multicast commit
   else __syncthreads();
   tc_fence_after();
+#if MQ_GEMM_UNIFORM
+  const uint32_t tmem_base = __shfl_sync(0xffffffffu, *reinterpret_cast<volatile uint32_t*>(tmem_slot), 0);
+#else
   const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(tmem_slot);
+#endif
 
   if (warp >= kEpiWarps) {
     reg_dealloc<40>();
@@ -285,7 +323,13 @@ mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
 #endif
       // without preload the first use of a TMEM stage finds it free (wait on the inverted parity); with preload the
       // epilogue's initial fill is completion #0 of the stage's empty barrier
-      constexpr uint32_t kEmptyFlip = kPreload ? 0u : 1u;
+      constexpr uint32_t kEmptyFlip = kRefill ? 0u : 1u;
+      const uint32_t idesc_fill = umma_idesc(1u, 0u, TM, BN);  // f16 x f16 -> f32
+      const uint32_t const_lo = umma_desc_lo(smem_u32(smem) + (uint32_t)L::kConstOffset);
+      auto fill = [&](uint32_t taddr) {
+        if (kPair) mma_const_fill_pair(taddr, const_lo, idesc_fill);
+        else mma_const_fill(taddr, const_lo, idesc_fill);
+      };
       const uint32_t smem_a = smem_u32(smem);
       const uint32_t full_a = smem_u32(full_bar), empty_a = smem_u32(empty_bar);
       const uint32_t tfull_a = smem_u32(tfull_bar), tempty_a = smem_u32(tempty_bar);
@@ -308,12 +352,13 @@ mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
               const uint32_t sa = smem_a + s * (uint32_t)L::kStageBytes;
               if (elect_one()) {
                 if (issue) {
+                  if (kMagicMma && b == 0) fill(tmem_base + t * BN);
                   if (kPair)
                     mma_i8_block4_pair(tmem_base + t * BN, umma_desc_lo(sa), umma_desc_lo(sa + L::kABytes), idesc_i8,
-                                       (kPreload || b > 0) ? 1u : 0u);
+                                       (kBiased || b > 0) ? 1u : 0u);
                   else
                     mma_i8_block4(tmem_base + t * BN, umma_desc_lo(sa), umma_desc_lo(sa + L::kABytes), idesc_i8,
-                                  (kPreload || b > 0) ? 1u : 0u);
+                                  (kBiased || b > 0) ? 1u : 0u);
                 }
                 commit(empty_a + s * 8u);                    // smem stage free once these MMAs have read it
                 if (b == bpu - 1) commit(tfull_a + t * 8u);  // accumulator stage complete -> epilogue
@@ -339,8 +384,9 @@ mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
                 for (int sub = 0; sub < spu; ++sub) {
                   const uint32_t off = (uint32_t)((h * spu + sub) * 2);
                   if (issue) {
-                    if (kPair) mma_i8_lo_pair(tmem_base + t * BN, la + off, lb + off, idesc_i8, (kPreload || sub > 0) ? 1u : 0u);
-                    else mma_i8_lo(tmem_base + t * BN, la + off, lb + off, idesc_i8, (kPreload || sub > 0) ? 1u : 0u);
+                    if (kMagicMma && sub == 0) fill(tmem_base + t * BN);
+                    if (kPair) mma_i8_lo_pair(tmem_base + t * BN, la + off, lb + off, idesc_i8, (kBiased || sub > 0) ? 1u : 0u);
+                    else mma_i8_lo(tmem_base + t * BN, la + off, lb + off, idesc_i8, (kBiased || sub > 0) ? 1u : 0u);
                   }
                 }
                 commit(tfull_a + t * 8u);
@@ -388,20 +434,34 @@ mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
     const int col0 = (ew >> 2) * CW;   // first tile column owned by this thread
     const int row = quarter * 32 + lane;
     // shared-window byte addresses (32-bit) of everything the unit loop touches: no generic-pointer arithmetic inside
+#if MQ_GEMM_UNIFORM >= 2
+    // lane-0 shuffles: warp-uniform AND opaque, so ptxas keeps the addresses in uniform registers instead of
+    // re-deriving the aligned shared-memory base (CgaCtaId, shifts, masks) three times per unit
+    auto uni = [](uint32_t v) { return __shfl_sync(0xffffffffu, v, 0); };
+    const uint32_t sscale_a = uni(smem_u32(sscale) + (uint32_t)col0 * 4u);
+    const uint32_t sas_a = uni(smem_u32(sscale) + (uint32_t)(BN + quarter * 32) * 4u) + (uint32_t)lane * 4u;
+    const uint32_t tfull_a = uni(smem_u32(tfull_bar)), tempty_a = uni(smem_u32(tempty_bar));
+    const uint32_t sfull_a = uni(smem_u32(sfull_bar)), sempty_a = uni(smem_u32(sempty_bar));
+#else
     const uint32_t sscale_a = smem_u32(sscale) + (uint32_t)col0 * 4u;
     const uint32_t sas_a = smem_u32(sscale) + (uint32_t)(BN + row) * 4u;
     const uint32_t tfull_a = smem_u32(tfull_bar), tempty_a = smem_u32(tempty_bar);
     const uint32_t sfull_a = smem_u32(sfull_bar), sempty_a = smem_u32(sempty_bar);
+#endif
     // a drained accumulator stage is handed back to the MMA issuer: the leader CTA's barrier in a pair
     const uint32_t tempty_l = kPair ? mapa_u32(tempty_a, 0u) : tempty_a;
     auto release_tmem = [tempty_l](uint32_t t) {
       if (kPair) mbar_arrive_cluster(tempty_l + t * 8u);
       else mbar_arrive_a(tempty_l + t * 8u);
     };
+#if MQ_GEMM_UNIFORM >= 2
+    const uint32_t tmem_lane = uni(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)col0);
+#else
     const uint32_t tmem_lane = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)col0;
+#endif
     uint32_t uc = 0, sc = 0;
     uint32_t magic[8];
-    if (kPreload) {
+    if (kRefill) {
 #pragma unroll
       for (int i = 0; i < 8; ++i) asm volatile("mov.u32 %0, 0x4B400000;" : "=r"(magic[i]));  // opaque: stays in registers
 #pragma unroll 1
@@ -437,24 +497,24 @@ mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
         const uint32_t ws_a = sscale_a + slot_off;
         const float as = __uint_as_float(__float_as_uint(as_raw) & 0xFFFFFFFCu);
         const float cas = -kMagic * as;
-        constexpr int CH = 16;  // columns per TMEM load (double buffered: 2 x CH registers)
+        constexpr int CH = MQ_GEMM_CH;  // columns per TMEM load (double buffered: 2 x CH registers)
         uint32_t v[2][CH];
 #ifdef MQ_DEBUG_NOLDTM
         const bool dbg_nomath = kProf && (p.debug & 4), dbg_noload = true;
 #else
         const bool dbg_nomath = kProf && (p.debug & 4), dbg_noload = kProf && (p.debug & 8);
 #endif
-        if (!dbg_noload) tmem_ld_32x16(taddr, v[0]);
+        if (!dbg_noload) tmem_ld_chunk(taddr, v[0]);
 #pragma unroll
         for (int c = 0; c < CW / CH; ++c) {
           tmem_ld_wait();
-          if (c + 1 < CW / CH && !dbg_noload) tmem_ld_32x16(taddr + (uint32_t)((c + 1) * CH), v[(c + 1) & 1]);
-          if (kPreload) {  // chunk c has been read: refill it
-            tmem_st_32x8(taddr + (uint32_t)(c * CH), magic);
-            tmem_st_32x8(taddr + (uint32_t)(c * CH + 8), magic);
+          if (c + 1 < CW / CH && !dbg_noload) tmem_ld_chunk(taddr + (uint32_t)((c + 1) * CH), v[(c + 1) & 1]);
+          if (kRefill) {  // chunk c has been read: refill it
+#pragma unroll
+            for (int r = 0; r < CH / 8; ++r) tmem_st_32x8(taddr + (uint32_t)(c * CH + r * 8), magic);
           }
           if (c + 1 == CW / CH) {  // every load of this thread has landed: hand the TMEM stage back to the MMA warp
-            if (kPreload) tmem_st_wait();
+            if (kRefill) tmem_st_wait();
             tc_fence_before();
             __syncwarp();
             if (lane == 0) release_tmem(t);
@@ -476,7 +536,7 @@ mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
             const float4 ws = lds_f32x4(ws_a + (uint32_t)((c * CH + q * 4) * 4));
 #endif
             const int j = q * 4;
-            constexpr uint32_t kAdd = kPreload ? 0u : kMagicBits;
+            constexpr uint32_t kAdd = kBiased ? 0u : kMagicBits;
             const float2 f0 = make_float2(__uint_as_float(vv[j + 0] + kAdd), __uint_as_float(vv[j + 1] + kAdd));
             const float2 f1 = make_float2(__uint_as_float(vv[j + 2] + kAdd), __uint_as_float(vv[j + 3] + kAdd));
             const float2 t0 = __ffma2_rn(f0, make_float2(as, as), make_float2(cas, cas));  // == v * as exactly
@@ -508,12 +568,12 @@ mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
         for (int c = 0; c < CW / 16; ++c) {
           tmem_ld_wait();
           if (c + 1 < CW / 16) tmem_ld_32x16(taddr + (uint32_t)((c + 1) * 16), v[(c + 1) & 1]);
-          if (kPreload && p.G > 0) {
+          if (kRefill && p.G > 0) {
             tmem_st_32x8(taddr + (uint32_t)(c * 16), magic);
             tmem_st_32x8(taddr + (uint32_t)(c * 16 + 8), magic);
           }
           if (c + 1 == CW / 16) {
-            if (kPreload) tmem_st_wait();
+            if (kRefill) tmem_st_wait();
             tc_fence_before();
             __syncwarp();
             if (lane == 0) release_tmem(t);

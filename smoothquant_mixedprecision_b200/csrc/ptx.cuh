@@ -316,6 +316,23 @@ __device__ __forceinline__ void mma_i8_lo(uint32_t tmem_d, uint32_t lo_a, uint32
       "r"(lo_a), "r"(lo_b), "r"(idesc), "r"(accumulate), "r"(kDescHiK128)
       : "memory");
 }
+// One kind::f16 MMA (K = 16) whose A and B descriptors both point at ONE 1024-byte constant atom with a stride of 0
+// between 8-row groups: every row of both operands reads the same 128 bytes, so D[m][n] = sum_k c_k * c_k for all
+// (m, n).  Used to set a whole accumulator stage to a constant without touching it from the epilogue threads.
+constexpr uint32_t kDescHiConst = 0x40004000u;  // SBO 0, version 1, SWIZZLE_128B
+#define MQ_MMA_CONST(NAME, GRP)                                                                                        \
+  __device__ __forceinline__ void NAME(uint32_t tmem_d, uint32_t lo, uint32_t idesc) {                                 \
+    asm volatile(                                                                                                      \
+        "{\n\t.reg .pred p;\n\t.reg .b64 da;\n\t"                                                                    \
+        "setp.ne.b32 p, 0, 0;\n\t"                                                                                     \
+        "mov.b64 da, {%1, %3};\n\t"                                                                                    \
+        "tcgen05.mma.cta_group::" GRP ".kind::f16 [%0], da, da, %2, p;\n\t}" ::"r"(tmem_d),                              \
+        "r"(lo), "r"(idesc), "r"(kDescHiConst)                                                                         \
+        : "memory");                                                                                                   \
+  }
+MQ_MMA_CONST(mma_const_fill, "1")
+MQ_MMA_CONST(mma_const_fill_pair, "2")
+#undef MQ_MMA_CONST
 __device__ __forceinline__ void tc_commit_a(uint32_t bar_addr) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar_addr) : "memory");
 }
