@@ -82,9 +82,11 @@ constexpr bool kPreload = MQ_GEMM_PRELOAD != 0;
 #ifndef MQ_GEMM_MAGIC_MMA
 #define MQ_GEMM_MAGIC_MMA 1
 #endif
-constexpr bool kMagicMma = MQ_GEMM_MAGIC_MMA != 0;
-constexpr bool kRefill = kPreload && !kMagicMma;       // the epilogue stores the pattern itself
-constexpr bool kBiased = kPreload || kMagicMma;        // drained words are the floats kMagic + sum
+// Chosen per launch (template parameter kMagicMma): units of up to 256 columns use the constant MMA, longer units keep
+// the epilogue refill (at g = 1024 the kernel is operand-stream bound and the extra MMA per unit costs 4-6 %).
+// MQ_GEMM_MAGIC_MMA / option gemm_magic_mma: 1 = by group size, 2 = always, 3 = never.
+constexpr int kMagicMmaMode = MQ_GEMM_MAGIC_MMA;
+constexpr int kMagicMmaMaxGroup = 256;
 #ifndef MQ_GEMM_UNIFORM
 #define MQ_GEMM_UNIFORM 2   // 0: plain thread-derived addresses (experiments), 1: uniform warp index, 2: + opaque uniform addresses
 #endif
@@ -117,7 +119,7 @@ struct SmemLayout {
   // per scale slot: ws[BN] | as[BM]   (fp32)
   static constexpr int kSlotFloats = BN + BM;
   static constexpr int kConstOffset = kStages * kStageBytes;  // 1024-byte constant atom (kMagicMma), 1024-aligned
-  static constexpr int kScaleOffset = kConstOffset + (kMagicMma ? 1024 : 0);
+  static constexpr int kScaleOffset = kConstOffset + 1024;
   static constexpr int kBarOffset = kScaleOffset + kScaleSlots * kSlotFloats * 4;
   // full[kStages], empty[kStages], tmem_full[2], tmem_empty[2], sfull[kScaleSlots], sempty[kScaleSlots], tmem base
   static constexpr int kBarBytes = (2 * kStages + 4 + 2 * kScaleSlots) * 8 + 16;
@@ -158,13 +160,15 @@ __device__ __forceinline__ long long wait_timed(bool prof, uint32_t bar, uint32_
   return ok ? clock64() - t : -1;
 }
 
-template <typename OutT, int BN, int kStages, bool kProf, bool kPair>
+template <typename OutT, int BN, int kStages, bool kProf, bool kPair, bool kMagicMma>
 __global__ void __launch_bounds__(kThreads, 1)
 mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_w,
                   const __grid_constant__ CUtensorMap map_as, const __grid_constant__ CUtensorMap map_ws,
                   const __grid_constant__ CUtensorMap map_sa, const __grid_constant__ CUtensorMap map_sw,
                   const GemmArgs p) {
   using L = SmemLayout<BN, kStages, kPair>;
+  constexpr bool kRefill = kPreload && !kMagicMma;  // the epilogue stores the pattern itself
+  constexpr bool kBiased = kPreload || kMagicMma;   // drained words are the floats kMagic + sum
   constexpr int CW = BN / kColSplit;  // columns per epilogue thread
   // work distribution: a CTA (or a CTA pair) loops over 128 (256) x BN tiles; `wid` / `wstride` index the workers
   const uint32_t cta_rank = kPair ? cluster_ctarank() : 0u;
@@ -719,14 +723,14 @@ int make_map(CUtensorMap* map, const void* ptr, CUtensorMapDataType dt, int esiz
   return MQ_OK;
 }
 
-template <typename OutT, int BN, int kStages, bool kPair = false>
-int launch_gemm(const CUtensorMap& ma, const CUtensorMap& mw, const CUtensorMap& mas, const CUtensorMap& mws,
-                const CUtensorMap& msa, const CUtensorMap& msw, GemmArgs p, cudaStream_t st) {
+template <typename OutT, int BN, int kStages, bool kPair, bool kMagicMma>
+int launch_gemm_m(const CUtensorMap& ma, const CUtensorMap& mw, const CUtensorMap& mas, const CUtensorMap& mws,
+                  const CUtensorMap& msa, const CUtensorMap& msw, GemmArgs p, cudaStream_t st) {
   using L = SmemLayout<BN, kStages, kPair>;
   p.debug = mq_get_option("gemm_debug", 0);
   p.profile = mq_get_option("gemm_profile", 0);
-  auto kern = p.profile ? mixed_gemm_kernel<OutT, BN, kStages, true, kPair>
-                        : mixed_gemm_kernel<OutT, BN, kStages, false, kPair>;
+  auto kern = p.profile ? mixed_gemm_kernel<OutT, BN, kStages, true, kPair, kMagicMma>
+                        : mixed_gemm_kernel<OutT, BN, kStages, false, kPair, kMagicMma>;
   MQ_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal));
   constexpr int TM = kPair ? 2 * BM : BM;
   p.tiles_m = (p.M + TM - 1) / TM;
@@ -754,6 +758,15 @@ int launch_gemm(const CUtensorMap& ma, const CUtensorMap& mw, const CUtensorMap&
   }
   MQ_CHECK_CUDA(cudaGetLastError());
   return MQ_OK;
+}
+
+template <typename OutT, int BN, int kStages, bool kPair = false>
+int launch_gemm(const CUtensorMap& ma, const CUtensorMap& mw, const CUtensorMap& mas, const CUtensorMap& mws,
+                const CUtensorMap& msa, const CUtensorMap& msw, const GemmArgs& p, cudaStream_t st) {
+  const int mode = mq_get_option("gemm_magic_mma", kMagicMmaMode);
+  const bool magic = mode == 2 || (mode == 1 && p.g <= kMagicMmaMaxGroup);
+  if (magic) return launch_gemm_m<OutT, BN, kStages, kPair, true>(ma, mw, mas, mws, msa, msw, p, st);
+  return launch_gemm_m<OutT, BN, kStages, kPair, false>(ma, mw, mas, mws, msa, msw, p, st);
 }
 
 template <typename OutT>
