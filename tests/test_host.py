@@ -76,3 +76,33 @@ def test_product_code_never_imports_the_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".cpp", ".h")):
                 src = open(os.path.join(dirpath, f)).read()
                 assert "oracle" not in src, os.path.join(dirpath, f)
+
+
+def test_packed_checkpoint_and_calibration_host_errors():
+    """Host-side behaviour of the components either side of the path (no GPU work): format / device checks of the
+    packed checkpoint, collectors refuse a CPU model, import paths of the shims."""
+    from smoothquant_mixedprecision_b200 import calibration, fake_quant as fq
+    from smoothquant.fake_quant import save_packed_model, load_packed_model          # exported through the shim
+    from smoothquant.calibration import get_act_scales as ref_sig
+    import inspect
+    assert save_packed_model is fq.save_packed_model and load_packed_model is fq.load_packed_model
+    assert list(inspect.signature(ref_sig).parameters) == ["model", "tokenizer", "dataset_path", "num_samples",
+                                                           "seq_len"]                   # calibration.py:13
+    meta = dict(format=fq.PACKED_FORMAT, in_features=8, out_features=4, group_size=4, quant_bits=4, mode="reference",
+                sort="max", act_quant="per_group", weight_quant="per_group", output_quant="None", int_groups=None,
+                int_fraction=None)
+    state = {"meta": meta, "bias": None, "salient_indices": None, "weight": torch.zeros(4, 8, dtype=torch.float16)}
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        fq.W4A4Linear.from_packed(state, "cpu")
+    with pytest.raises(ValueError, match="format"):
+        fq.W4A4Linear.from_packed({**state, "meta": {**meta, "format": 0}}, "cuda")
+    with pytest.raises(ValueError, match="format"):
+        fq.load_packed_model(torch.nn.Linear(2, 2), {"format": 0, "linears": {}, "rest": {}})
+    with torch.device("meta"):
+        skeleton = torch.nn.Sequential(torch.nn.Linear(2, 2))
+    with pytest.raises(ValueError, match="materialised"):
+        fq.load_packed_model(skeleton, {"format": fq.PACKED_FORMAT, "linears": {}, "rest": {}})
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        calibration.get_act_scales(torch.nn.Sequential(torch.nn.Linear(4, 4)), [torch.zeros(1, 4)])
+    with pytest.raises(ValueError):
+        calibration.collect_sort_keys(torch.nn.Linear(2, 2), [], "median")
