@@ -93,6 +93,10 @@ constexpr int kMagicMmaMaxGroup = 256;
 #ifndef MQ_GEMM_CH
 #define MQ_GEMM_CH 16
 #endif
+#ifndef MQ_GEMM_SCALE_ON_FULL
+#define MQ_GEMM_SCALE_ON_FULL 1
+#endif
+constexpr bool kScaleOnFull = MQ_GEMM_SCALE_ON_FULL != 0;
 __device__ __forceinline__ void tmem_ld_chunk(uint32_t taddr, uint32_t (&v)[16]) { tmem_ld_32x16(taddr, v); }
 __device__ __forceinline__ void tmem_ld_chunk(uint32_t taddr, uint32_t (&v)[32]) { tmem_ld_32x32(taddr, v); }
 #ifndef MQ_GEMM_PAIR_DEFAULT
@@ -265,28 +269,41 @@ mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
         const int nw = n0 + (int)cta_rank * L::kBRows;  // first W row this CTA stages
         int u_next = 0;  // next integer unit whose scale vectors have not been requested yet
         for (int kb = 0; kb < kb_total; ++kb, ++kbc) {
-          // scale vectors of every unit that starts inside this K block: ws[u, n0 .. n0+BN) and as[u, m0 .. m0+BM)
-          while (u_next < p.G && u_next * p.g < (kb + 1) * 128) {
-            const uint32_t slot = sc % kScaleSlots;
-            if (!mbar_wait(&sempty_bar[slot], ((sc / kScaleSlots) & 1u) ^ 1u, 0x600u + slot)) goto teardown;
-            float* sl = sscale + slot * L::kSlotFloats;
-            if (elect_one()) {
-              mbar_expect_tx(&sfull_bar[slot], (uint32_t)(L::kSlotFloats * 4));
-              tma_load_2d(sl, &map_sw, n0, u_next, &sfull_bar[slot]);
-              tma_load_2d(sl + BN, &map_sa, m0, u_next, &sfull_bar[slot]);
-            }
-            ++u_next;
-            ++sc;
-          }
           const uint32_t s = kbc % kStages, ph = (kbc / kStages) & 1u;
           if ((dt = wait_timed<kProf>(prof, smem_u32(&empty_bar[s]), ph ^ 1u, 0x200u + s)) < 0) goto teardown;
           if (kProf) w0 += dt;
+          // Scale vectors of every unit that starts inside this K block (ws[u, n0 .. n0+BN) and as[u, m0 .. m0+BM))
+          // complete on the SAME full barrier as the block's operands (MQ_GEMM_SCALE_ON_FULL): the MMAs of the unit
+          // cannot start before they have landed, so the accumulator-complete barrier the epilogue waits for anyway
+          // also covers the scales and the epilogue needs no second wait per unit.
+          const uint32_t sc0 = sc;
+          while (u_next < p.G && u_next * p.g < (kb + 1) * 128) {
+            const uint32_t slot = sc % kScaleSlots;
+            if (!mbar_wait(&sempty_bar[slot], ((sc / kScaleSlots) & 1u) ^ 1u, 0x600u + slot)) goto teardown;
+            ++u_next;
+            ++sc;
+          }
+          const uint32_t n_new = sc - sc0;
+          const int u0 = u_next - (int)n_new;
           unsigned char* sa = smem + (size_t)s * L::kStageBytes;
           unsigned char* sb = sa + L::kABytes;
           if (elect_one()) {
+            const uint32_t scale_bytes = kScaleOnFull ? n_new * (uint32_t)(L::kSlotFloats * 4) : 0u;
             if (kPair) {  // both CTAs' bytes complete on the leader's barrier, which the leader arms for both
-              if (leader) mbar_expect_tx(&full_bar[s], (uint32_t)(2 * L::kStageBytes));
+              if (leader) mbar_expect_tx(&full_bar[s], 2u * ((uint32_t)L::kStageBytes + scale_bytes));
               const uint32_t fb = full_leader + s * 8u;
+              for (uint32_t q = 0; q < n_new; ++q) {
+                float* sl = sscale + ((sc0 + q) % kScaleSlots) * L::kSlotFloats;
+                if (kScaleOnFull) {
+                  tma_load_2d_pair(sl, &map_sw, n0, u0 + (int)q, fb);
+                  tma_load_2d_pair(sl + BN, &map_sa, m0, u0 + (int)q, fb);
+                } else {
+                  uint64_t* sf = &sfull_bar[(sc0 + q) % kScaleSlots];
+                  mbar_expect_tx(sf, (uint32_t)(L::kSlotFloats * 4));
+                  tma_load_2d(sl, &map_sw, n0, u0 + (int)q, sf);
+                  tma_load_2d(sl + BN, &map_sa, m0, u0 + (int)q, sf);
+                }
+              }
               if (kb < p.kb_int) {
                 tma_load_2d_pair(sa, &map_a, kb * 128, m0, fb);
                 tma_load_2d_pair(sb, &map_w, kb * 128, nw, fb);
@@ -296,7 +313,14 @@ mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
                 tma_load_2d_pair(sb, &map_ws, ks, nw, fb);
               }
             } else {
-              mbar_expect_tx(&full_bar[s], (uint32_t)L::kStageBytes);
+              mbar_expect_tx(&full_bar[s], (uint32_t)L::kStageBytes + scale_bytes);
+              for (uint32_t q = 0; q < n_new; ++q) {
+                float* sl = sscale + ((sc0 + q) % kScaleSlots) * L::kSlotFloats;
+                uint64_t* sf = kScaleOnFull ? &full_bar[s] : &sfull_bar[(sc0 + q) % kScaleSlots];
+                if (!kScaleOnFull) mbar_expect_tx(sf, (uint32_t)(L::kSlotFloats * 4));
+                tma_load_2d(sl, &map_sw, n0, u0 + (int)q, sf);
+                tma_load_2d(sl + BN, &map_sa, m0, u0 + (int)q, sf);
+              }
               if (kb < p.kb_int) {
                 tma_load_2d(sa, &map_a, kb * 128, m0, &full_bar[s]);
                 tma_load_2d(sb, &map_w, kb * 128, n0, &full_bar[s]);
@@ -491,12 +515,14 @@ mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
       for (int u = 0; u < p.G; ++u, ++uc, ++sc) {
         const uint32_t t = uc & 1u, slot = sc % kScaleSlots;
         const uint32_t slot_off = slot * (uint32_t)(L::kSlotFloats * 4);
-        if ((dt = wait_timed<kProf>(prof, sfull_a + slot * 8u, (sc / kScaleSlots) & 1u, 0x700u + slot)) < 0) goto teardown;
-        if (kProf) w1 += dt;
-        const float as_raw = lds_f32(sas_a + slot_off);  // consumed after the accumulator wait below
+        if (!kScaleOnFull) {
+          if ((dt = wait_timed<kProf>(prof, sfull_a + slot * 8u, (sc / kScaleSlots) & 1u, 0x700u + slot)) < 0) goto teardown;
+          if (kProf) w1 += dt;
+        }
         if ((dt = wait_timed<kProf>(prof, tfull_a + t * 8u, (uc >> 1) & 1u, 0x500u + t)) < 0) goto teardown;
         if (kProf) w0 += dt;
         tc_fence_after();
+        const float as_raw = lds_f32(sas_a + slot_off);  // landed before the unit's MMAs could start (kScaleOnFull)
         const uint32_t taddr = tmem_lane + t * BN;
         const uint32_t ws_a = sscale_a + slot_off;
         const float as = __uint_as_float(__float_as_uint(as_raw) & 0xFFFFFFFCu);
