@@ -3,7 +3,9 @@ import sys, os, json
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 import torch
-from smoothquant_mixedprecision_b200 import ops
+from smoothquant_mixedprecision_b200 import ops, _lib
+if os.environ.get('MQ_RPS'): _lib.set_option('quant_rows_per_stage', int(os.environ['MQ_RPS']))
+if os.environ.get('MQ_QWARPS'): _lib.set_option('quant_warps', int(os.environ['MQ_QWARPS']))
 M, K, g = (int(v) for v in sys.argv[1:4]); p = float(sys.argv[4])
 torch.manual_seed(0)
 x = (torch.randn(M, K, device="cuda") * torch.exp(0.5 * torch.randn(K, device="cuda"))).half()
