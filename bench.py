@@ -13,6 +13,12 @@ random-init weights.  N > 1: one replica per GPU, data-parallel over sequences, 
           last output -> host, all inside the timed region
 `roofline` of the dominant kernel (mixed GEMM), CUDA events around every launch inside the timed region
 `cpu_baseline` the CPU oracle port of the reference layer on a bounded sample (rank 0, N = 1 only)
+`gpu_reference` / `fp16_cublas`  (N = 1) the reference's fake-quant forward arithmetic (fake_quant.py:280-322) written
+          with stock PyTorch CUDA ops, and plain fp16 F.linear, over one decoder layer's 7 linears at the full 32 768
+          tokens on the same GPU (x 32 layers): the like-for-like GPU baselines of SURVEY 8(d)
+`gemm_tops` (N = 1) the isolated mixed GEMM at the three Llama-2-7B linear shapes, M = 32 768
+`column_parallel` (N > 1) the same 224 linears sharded over out_features across the N GPUs (strong scaling of ONE
+          32 768-token batch, NCCL all-gathers where the consumer needs the full width), with the comm / compute split
 `--impl reference` times that CPU path alone (all host threads) and prints the same line with "impl": "reference".
 """
 import argparse
@@ -46,8 +52,10 @@ def parse():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--tokens", type=int, default=16 * 2048, help="tokens per GPU per step")
     ap.add_argument("--layers", type=int, default=LAYERS)
-    ap.add_argument("--cpu-tokens", type=int, default=1024, help="tokens of the bounded CPU sample")
+    ap.add_argument("--cpu-tokens", type=int, default=4096, help="tokens of the bounded CPU sample")
+    ap.add_argument("--cpu-layers", type=int, default=2, help="decoder layers of the bounded CPU sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-gpu-baselines", action="store_true")
     ap.add_argument("--parallel", default="dp", choices=["dp", "tp"],
                     help="N > 1: dp = one replica per GPU over different sequences (weak scaling, no collective); "
                          "tp = column-parallel over out_features with NCCL all-gathers (strong scaling)")
@@ -59,36 +67,41 @@ def ops_per_token(layers):
 
 
 # ---------------------------------------------------------------------------------------------- CPU arm (oracle)
-def cpu_layer_sample(tokens, threads):
-    """One decoder layer's 7 linears through the oracle's literal reference layer (fp32, like the reference's own CPU
-    runs, examples/group_size_analysis.py:62-66).  Returns a closure running one pass and the setup seconds."""
+def cpu_layer_sample(tokens, threads, n_layers):
+    """`n_layers` decoder layers' 7 linears each through the oracle's literal reference layer (fp32, like the
+    reference's own CPU runs, examples/group_size_analysis.py:62-66).  Returns a closure running one pass and the setup
+    seconds."""
     import torch
     from oracle import mq_oracle as O
     torch.set_num_threads(threads)
     g = torch.Generator().manual_seed(0)
     t0 = time.perf_counter()
-    layers = {}
     xs = {K: torch.randn(tokens, K, generator=g) * torch.exp(0.5 * torch.randn(K, generator=g))
           for K in (HIDDEN, INTER)}
-    for name, (N, K) in SHAPES.items():
-        w = torch.randn(N, K, generator=g) / K ** 0.5
-        imp = xs[K].abs().mean(dim=0)
-        sal = O.select_salient(imp, SALIENT)
-        layers[name] = (O.w4a4_weight_reference(w, sal, 4, GROUP), sal, K)
+    stack = []
+    for _ in range(n_layers):
+        layers = {}
+        for name, (N, K) in SHAPES.items():
+            w = torch.randn(N, K, generator=g) / K ** 0.5
+            imp = xs[K].abs().mean(dim=0)
+            sal = O.select_salient(imp, SALIENT)
+            layers[name] = (O.w4a4_weight_reference(w, sal, 4, GROUP), sal, K)
+        stack.append(layers)
     setup = time.perf_counter() - t0
 
     def run():
         out = None
-        for name, (wq, sal, K) in layers.items():
-            out = O.w4a4_forward_reference(xs[K], wq, None, sal, 4, GROUP)
+        for layers in stack:
+            for name, (wq, sal, K) in layers.items():
+                out = O.w4a4_forward_reference(xs[K], wq, None, sal, 4, GROUP)
         return out
     return run, setup
 
 
-def time_cpu(tokens, steps, warmup):
+def time_cpu(tokens, steps, warmup, n_layers=2):
     import torch
     threads = os.cpu_count() or 1
-    run, setup = cpu_layer_sample(tokens, threads)
+    run, setup = cpu_layer_sample(tokens, threads, n_layers)
     for _ in range(warmup):
         run()
     ts = []
@@ -96,10 +109,12 @@ def time_cpu(tokens, steps, warmup):
         t0 = time.perf_counter()
         run()
         ts.append(time.perf_counter() - t0)
-    per_layer = sum(ts) / len(ts)
+    per_layer = sum(ts) / len(ts) / n_layers
     return {"tok_s": tokens / (per_layer * LAYERS), "s_per_layer": per_layer, "threads": threads, "setup_s": setup,
-            "sample": f"1 of {LAYERS} decoder layers (7 linears), {tokens} tokens, fp32, oracle port of "
-                      f"W4A4Linear.forward; tokens/s = tokens / (t_layer * {LAYERS})",
+            "sample": f"{n_layers} of {LAYERS} decoder layers (7 linears each), {tokens} tokens, fp32, oracle port of "
+                      f"W4A4Linear.forward; tokens/s = tokens / (t_layer * {LAYERS}) -- every layer has the same "
+                      f"shapes and the layer is row-independent apart from the column abs-max, so time is linear in "
+                      f"layers and tokens",
             "torch_threads": torch.get_num_threads()}
 
 
@@ -107,10 +122,20 @@ def reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    r = time_cpu(args.cpu_tokens, max(1, args.steps), max(0, args.warmup))
+    # bounded sample: the largest of (layers, tokens) whose (steps + warmup) passes fit ~150 s on this host, sized from
+    # a probe pass of 1 layer x 1024 tokens (time is linear in both, see `sample`)
+    steps, warmup = max(1, args.steps), max(0, args.warmup)
+    probe = time_cpu(1024, 1, 1, 1)
+    t_probe = probe["s_per_layer"]
+    tokens, n_layers = 1024, 1
+    for cand_layers, cand_tokens in ((args.cpu_layers, args.cpu_tokens), (1, args.cpu_tokens), (1, 2048)):
+        if t_probe * (cand_tokens / 1024.0) * cand_layers * (steps + warmup) <= 150.0:
+            tokens, n_layers = cand_tokens, cand_layers
+            break
+    r = time_cpu(tokens, steps, warmup, n_layers)
     line = {"impl": "reference", "metric": METRIC, "value": r["tok_s"], "unit": "tokens/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["s_per_layer"] * LAYERS * 1e3 *
-            (args.tokens / args.cpu_tokens), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            (args.tokens / tokens), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
             "config": {"workload": "Llama-2-7B W4A4 linears g=128 5% salient, CPU fake-quant path", "tokens_per_step":
                        args.tokens, "group_size": GROUP, "salient_prop": SALIENT},
@@ -159,6 +184,100 @@ class ClockSampler:
         busy = [c for c in clocks if mx and c > 0.3 * mx] or clocks
         return {"sm_mhz": statistics.median(busy) if busy else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
                 "samples": len(clocks)}
+
+
+# ---------------------------------------------------------------------------------------------- GPU baselines
+def torch_reference_forward(x, wq, keep_mask, g):
+    """The reference layer's forward arithmetic (fake_quant.py:291-306 -> :105-154) with stock PyTorch CUDA ops:
+    boolean-mask compaction of the non-salient columns, per-call column abs-max, argsort, gather, zero pad, per-group
+    abs-max scale, div / round / mul in place, inverse permutation, scatter back, F.linear on the fake-quantised fp16
+    operands.  Baseline only -- nothing of this repo's kernels runs here."""
+    import torch
+    import torch.nn.functional as F
+    t = x[:, keep_mask]
+    perm = torch.argsort(t.abs().amax(dim=0))
+    tp = t[:, perm]
+    C = tp.shape[1]
+    G = -(-C // g)
+    if G * g != C:
+        tp = F.pad(tp, (0, G * g - C))
+    tg = tp.view(tp.shape[0], G, g)
+    sc = tg.abs().amax(dim=-1, keepdim=True).clamp_(min=1e-5).div_(7)
+    tg.div_(sc).round_().mul_(sc)
+    q = x.clone()
+    q[:, keep_mask] = tp[:, :C][:, torch.argsort(perm)]
+    return F.linear(q, wq)
+
+
+def gpu_baselines(mods, x0, steps=3):
+    """One decoder layer's 7 linears at the full token count: (a) the reference's fake-quant arithmetic under stock
+    PyTorch, (b) plain fp16 F.linear (cuBLAS).  Returns seconds per decoder layer for each."""
+    import torch
+    import torch.nn.functional as F
+    dev = x0.device
+    ws, masks = {}, {}
+    for name, m in mods.items():
+        ws[name] = m.weight.contiguous()              # fake-quantised fp16 weight [N, K] (dequantised view)
+        mask = torch.ones(m.in_features, dtype=torch.bool, device=dev)
+        mask[m.sal_sorted.long()] = False
+        masks[name] = mask
+
+    def chain(fn):
+        x = x0
+        fn("q_proj", x)
+        fn("k_proj", x)
+        v = fn("v_proj", x)
+        o = fn("o_proj", v)
+        fn("gate_proj", o)
+        u = fn("up_proj", o)
+        return fn("down_proj", u)
+
+    def timeit(fn):
+        chain(fn)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            chain(fn)
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) * 1e-3 / steps
+
+    t_ref = timeit(lambda n, x: torch_reference_forward(x, ws[n], masks[n], GROUP))
+    t_fp16 = timeit(lambda n, x: F.linear(x, ws[n]))
+    return t_ref, t_fp16
+
+
+def isolated_gemm_tops(mods, x_by_k, iters=10):
+    """The mixed GEMM alone (activation already quantised) at the three Llama-2-7B linear shapes, M = tokens."""
+    import torch
+    from smoothquant_mixedprecision_b200 import ops
+    out = {}
+    for name in ("q_proj", "gate_proj", "down_proj"):
+        m = mods[name]
+        x = x_by_k[m.in_features]
+        a = ops.quant_rows(x, m.perm, m.sal_sorted, m.group_size, m.quant_bits, Kn=m.perm.numel(),
+                           int_groups=m.int_groups)
+        w = ops.QuantizedRows(codes=m.w_codes, scales=m.w_scales, sal=m.w_sal, rows=m.out_features, Kn=a.Kn, Ks=a.Ks,
+                              group_size=m.group_size, int_groups=a.int_groups)
+        for _ in range(3):
+            ops.mixed_gemm(a, w, None)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(iters):
+            ops.mixed_gemm(a, w, None)
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / iters
+        M, N, K = x.shape[0], m.out_features, m.in_features
+        out[f"{M}x{N}x{K}"] = {"ms": ms, "tops": 2.0 * M * N * K / (ms * 1e-3) / 1e12}
+    return out
+
+
+# tcgen05 issue-rate ceilings measured with back-to-back MMAs on all SMs (tools/ubench.cu, profiles/r01_ubench.log)
+UBENCH = {"i8_tops": 4260.0, "f16_tflops": 1666.0, "at_mhz": 1831.0}
+NOMINAL = {"i8_tops": 4500.0, "f16_tflops": 2250.0}
 
 
 def build_stack(layers, tokens, dev, seed, tp=None):
@@ -294,6 +413,18 @@ def gpu_arm(args):
     t_roof_ms = (ops_i8 / (2 * bf16 * 1e12) + ops_f16 / (bf16 * 1e12)) * 1e3
     achieved = (ops_i8 + ops_f16) / (gemm_ms * 1e-3) / 1e12
     peak_mix = (ops_i8 + ops_f16) / (t_roof_ms * 1e-3) / 1e12
+
+    def frac_against(p_i8, p_f16):          # same serial-pipe roofline with other peak pairs (TOP/s)
+        return ((ops_i8 / (p_i8 * 1e12) + ops_f16 / (p_f16 * 1e12)) * 1e3) / gemm_ms
+
+    clk = (clocks or {}).get("sm_mhz") or UBENCH["at_mhz"]
+    ub_scale = clk / UBENCH["at_mhz"]
+    fractions = {
+        "vs_2x_bf16_sustained_measured": frac_against(2 * bf16, bf16),
+        "vs_tcgen05_ubench_at_bench_clock": frac_against(UBENCH["i8_tops"] * ub_scale, UBENCH["f16_tflops"] * ub_scale),
+        "vs_nominal_4500_2250": frac_against(NOMINAL["i8_tops"], NOMINAL["f16_tflops"]),
+        "ubench_source": "tools/ubench.cu back-to-back tcgen05.mma on 148 SMs: kind::i8 4260 TOP/s, kind::f16 1666 "
+                         f"TFLOP/s at 1831 MHz, scaled to the median SM clock of this run ({clk} MHz)"}
     line = {"metric": METRIC, "value": job_tokens / (ms * 1e-3), "unit": "tokens/s", "n_gpus": world,
             "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": ms, "higher_is_better": True,
             "scaling": "strong" if tp else "weak", "vs_baseline": None,
@@ -311,7 +442,10 @@ def gpu_arm(args):
             "roofline": {"kernel": "mixed_gemm_kernel", "bound": "tensor", "achieved": achieved, "peak": peak_mix,
                          "unit": "TOP/s", "frac": achieved / peak_mix, "traffic": traffic.get("mixed_gemm_kernel"),
                          "traffic_unit": "DRAM bytes per launch (ncu, profiles/*_traffic.json)", "peak_source": peak_src,
-                         "share_of_step": gemm_ms / ms, "launches_per_step": len(ev) // args.steps},
+                         "share_of_step": gemm_ms / ms, "launches_per_step": len(ev) // args.steps,
+                         "fractions": fractions,
+                         "ops_note": "ops = 2*M*N*Kn on the int8 pipe (true quantised columns, no padding) + 2*M*N*Ks "
+                                     "on the f16 pipe"},
             "roofline_quantiser": {"kernel": "quant_rows_fast", "bound": "hbm",
                                    "achieved": quant_bytes / (quant_ms * 1e-3) / 1e9,
                                    "peak": peaks.get("hbm_gbs") or 6500.0, "unit": "GB/s",
@@ -321,8 +455,20 @@ def gpu_arm(args):
                                    "share_of_step": quant_ms / ms,
                                    "launches_per_step": len(qev) // args.steps},
             "clocks": clocks}
+    if world == 1 and not args.no_gpu_baselines:
+        xk = {HIDDEN: x0, INTER: torch.randn(M, INTER, device=dev, dtype=torch.float16)}
+        line["gemm_tops"] = isolated_gemm_tops(stack[0], xk)
+        del xk
+        t_ref, t_fp16 = gpu_baselines(stack[0], x0)
+        line["gpu_reference"] = {
+            "value": M / (t_ref * LAYERS), "unit": "tokens/s", "ms_per_decoder_layer": t_ref * 1e3,
+            "what": "the reference's fake-quant W4A4Linear.forward arithmetic (fake_quant.py:280-322) under stock "
+                    "PyTorch CUDA ops, fp16, 1 decoder layer (7 linears) x 32768 tokens, x 32"}
+        line["fp16_cublas"] = {
+            "value": M / (t_fp16 * LAYERS), "unit": "tokens/s", "ms_per_decoder_layer": t_fp16 * 1e3,
+            "what": "plain fp16 F.linear (cuBLAS) on the same 7 shapes x 32768 tokens, x 32"}
     if world == 1 and not args.no_cpu_baseline:
-        r = time_cpu(args.cpu_tokens, 2, 1)
+        r = time_cpu(args.cpu_tokens, 2, 1, args.cpu_layers)
         line["cpu_baseline"] = {"value": r["tok_s"], "unit": "tokens/s", "cores": r["threads"], "kind": "port",
                                 "sample": r["sample"]}
     print(json.dumps(line), flush=True)

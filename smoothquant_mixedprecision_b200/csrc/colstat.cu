@@ -182,6 +182,14 @@ int dispatch_kind(int kind, const void* x, int64_t M, int64_t K, int64_t ld, flo
 // parallel and stable by construction; n <= 65535 keys (28 672 for Llama-2-70B) is ~1e9 compares at most.
 constexpr int kSortTile = 2048;
 
+// total order on the keys: NaN compares false with everything, which would give every NaN key the same rank and
+// leave output slots unwritten.  NaN is ordered like torch.argsort orders it -- above +inf (last when ascending,
+// first when descending) -- by mapping it to +inf before the optional negation; ties fall back to the index.
+__device__ __forceinline__ float sort_canon(float k, int descending) {
+  if (k != k) k = __int_as_float(0x7f800000);
+  return descending ? -k : k;
+}
+
 __global__ void __launch_bounds__(256)
 argsort_rank_kernel(const float* __restrict__ key, const int32_t* __restrict__ subset, int n, int descending,
                     int32_t* __restrict__ out) {
@@ -192,8 +200,7 @@ argsort_rank_kernel(const float* __restrict__ key, const int32_t* __restrict__ s
   float ki = 0.f;
   if (live) {
     id = subset ? subset[i] : i;
-    ki = key[id];
-    if (descending) ki = -ki;
+    ki = sort_canon(key[id], descending);
   }
   int rank = 0;
   for (int base = 0; base < n; base += kSortTile) {
@@ -201,8 +208,7 @@ argsort_rank_kernel(const float* __restrict__ key, const int32_t* __restrict__ s
     __syncthreads();
     for (int t = threadIdx.x; t < cnt; t += blockDim.x) {
       int jd = subset ? subset[base + t] : base + t;
-      float kj = key[jd];
-      sk[t] = descending ? -kj : kj;
+      sk[t] = sort_canon(key[jd], descending);
     }
     __syncthreads();
     if (live) {

@@ -48,11 +48,23 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
 }
 
 // Fault record of this translation unit: [0] code (0 = none), [1] block, [2] thread, [3] parity, [4] spins>>10.
-// A wait that does not complete within kWaitLimitNs records itself here and returns false; every other wait in
-// the grid then gives up quickly too, so a broken pipeline ends the kernel instead of hanging the GPU.  The host
-// reads (and clears) the record with the TU's own mq_*_fault() helper.
+// A wait that does not complete within kWaitLimitNs records itself here and then TRAPS: the launch ends with a sticky
+// CUDA error that the next synchronising call of the host (torch) raises, so a broken pipeline can neither hang the
+// GPU nor hand back uninitialised outputs silently.  The record survives the trap only for a debugger; hosts that
+// want it read it with the TU's own mq_*_fault() helper before the context is torn down.
 static __device__ unsigned int g_mq_fault[8];
-constexpr unsigned long long kWaitLimitNs = 2000ull * 1000ull * 1000ull;
+constexpr unsigned long long kWaitLimitNs = 5000ull * 1000ull * 1000ull;
+
+static __device__ __noinline__ void mq_wait_expired(uint32_t parity, uint32_t code, uint32_t spins) {
+  if (atomicCAS(&g_mq_fault[0], 0u, code) == 0u) {
+    g_mq_fault[1] = blockIdx.x + (blockIdx.y << 16);
+    g_mq_fault[2] = threadIdx.x;
+    g_mq_fault[3] = parity;
+    g_mq_fault[4] = spins >> 10;
+    __threadfence_system();
+  }
+  __trap();
+}
 
 __device__ __forceinline__ unsigned long long globaltimer_ns() {
   unsigned long long t;
@@ -67,15 +79,8 @@ static __device__ __forceinline__ bool mbar_wait_slow(uint64_t* bar, uint32_t pa
   while (!mbar_try_wait(bar, parity)) {
     if ((++spins & 0x3FFu) == 0) {
       if (spins == 0x400u) t0 = globaltimer_ns();
-      const bool aborted = *reinterpret_cast<volatile unsigned int*>(&g_mq_fault[0]) != 0;
-      if (aborted || globaltimer_ns() - t0 > kWaitLimitNs) {
-        if (atomicCAS(&g_mq_fault[0], 0u, code) == 0u) {
-          g_mq_fault[1] = blockIdx.x + (blockIdx.y << 16);
-          g_mq_fault[2] = threadIdx.x;
-          g_mq_fault[3] = parity;
-          g_mq_fault[4] = spins >> 10;
-          __threadfence();
-        }
+      if (globaltimer_ns() - t0 > kWaitLimitNs) {
+        mq_wait_expired(parity, code, spins);
         return false;
       }
     }
@@ -109,15 +114,8 @@ static __device__ __forceinline__ bool mbar_wait_slow_a(uint32_t bar_addr, uint3
   while (!mbar_try_wait_a(bar_addr, parity)) {
     if ((++spins & 0x3FFu) == 0) {
       if (spins == 0x400u) t0 = globaltimer_ns();
-      const bool aborted = *reinterpret_cast<volatile unsigned int*>(&g_mq_fault[0]) != 0;
-      if (aborted || globaltimer_ns() - t0 > kWaitLimitNs) {
-        if (atomicCAS(&g_mq_fault[0], 0u, code) == 0u) {
-          g_mq_fault[1] = blockIdx.x + (blockIdx.y << 16);
-          g_mq_fault[2] = threadIdx.x;
-          g_mq_fault[3] = parity;
-          g_mq_fault[4] = spins >> 10;
-          __threadfence();
-        }
+      if (globaltimer_ns() - t0 > kWaitLimitNs) {
+        mq_wait_expired(parity, code, spins);
         return false;
       }
     }

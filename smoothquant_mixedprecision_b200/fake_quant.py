@@ -24,6 +24,7 @@ ascending index and accepts an explicit permutation where parity against a recor
 """
 from __future__ import annotations
 
+import threading
 from typing import Dict, Optional
 
 import torch
@@ -99,6 +100,8 @@ def quantize_activation_per_group_absmax_sort(t, n_bits, group_size=128, perm=No
     ``perm`` (optional, extension) replays a recorded permutation instead of computing one."""
     if perm is None:
         perm = _dynamic_perm(t.reshape(-1, t.shape[-1]))
+    else:
+        _validate_columns(perm, t.shape[-1], "perm")
     return ops.fakequant_rows(t, perm, group_size, n_bits)
 
 
@@ -107,18 +110,29 @@ def quantize_weight_per_group_absmax_sort(w, n_bits, group_size=128, perm=None):
     """fake_quant.py:157-207 -- the same algorithm on w [N, K]; the key is the per-input-column max over rows."""
     if perm is None:
         perm = _dynamic_perm(w)
+    else:
+        _validate_columns(perm, w.shape[-1], "perm")
     return ops.fakequant_rows(w, perm, group_size, n_bits)
 
 
 # ------------------------------------------------------------------------------------------- the layer
-# One-entry cache of the last quantised activation: (input tensor kept alive, its version, partition id) -> K1 output.
-# Keeping the input alive pins its address, so pointer + version identify its contents (torch ops bump the version;
-# the in-place quantisers of this package bump it explicitly).
-_ACT_CACHE = {"key": None, "x": None, "a": None, "hits": 0}
+# Quantised-activation sharing between layers fed by the SAME tensor with the same K partition (q/k/v, gate/up: the
+# reference's calibration hooks give them identical statistics, fake_quant.py:396-455): K1 runs once, the others reuse
+# its output.  One entry per (device, CUDA stream): a hit can only happen on the stream that produced the entry, so
+# the consumer is stream-ordered behind the producer without an event.  An entry is identified by the identity of the
+# tensor object the caller passed (kept alive, so neither its id nor its address can be recycled), its version counter
+# when it has one (inference tensors do not: there the caller must not mutate a tensor between the calls of one
+# group, which no decoder layer does) and the partition id.  Walkers tell each layer how many layers share its input
+# (`_share_n`); the entry is dropped when the last of them has consumed it, so nothing stays pinned after a model
+# forward.  Layers built one by one (`_share_n` unset) keep the classic behaviour: the entry lives until the next
+# miss on that stream, or until clear_act_cache().
+_ACT_CACHE = {"hits": 0, "entries": {}}
+_ACT_LOCK = threading.Lock()
 
 
 def clear_act_cache():
-    _ACT_CACHE.update(key=None, x=None, a=None)
+    with _ACT_LOCK:
+        _ACT_CACHE["entries"].clear()
 
 
 # Share of the K groups that run as integer codes (tcgen05 kind::i8 + per-group fp32 rescale on the CUDA cores); the
@@ -143,17 +157,52 @@ def _int_groups(G, g, frac):
     return max(0, min(G, gi))
 
 
-def _shared_act(xin, mod):
+def _version_of(t):
+    try:
+        return None if t.is_inference() else t._version
+    except RuntimeError:            # no version counter: identity of the object is all there is
+        return None
+
+
+def _shared_act(x_orig, xin, mod):
+    """K1 output for `xin` (= x_orig as a 2-D tensor of the compute dtype), shared within a group of layers."""
     pid = getattr(mod, "_partition_id", None)
-    key = (xin.data_ptr(), xin._version, tuple(xin.shape), xin.stride(), xin.dtype, xin.device, pid)
-    if pid is not None and _ACT_CACHE["key"] == key:
-        _ACT_CACHE["hits"] += 1
-        return _ACT_CACHE["a"]
+    share = getattr(mod, "_share_n", None)
+    dev = xin.device
+    slot = (dev.index, torch.cuda.current_stream(dev).cuda_stream)
+    sig = (_version_of(x_orig), xin.data_ptr(), tuple(xin.shape), xin.stride(), xin.dtype, pid)
+    if pid is not None:
+        with _ACT_LOCK:
+            e = _ACT_CACHE["entries"].get(slot)
+            if e is not None and e["x"] is x_orig and e["sig"] == sig:
+                _ACT_CACHE["hits"] += 1
+                a = e["a"]
+                if e["left"] is not None:
+                    e["left"] -= 1
+                    if e["left"] <= 0:
+                        del _ACT_CACHE["entries"][slot]
+                return a
     a = ops.quant_rows(xin, mod.perm, mod.sal_sorted, mod.group_size, mod.quant_bits,
                        Kn=0 if mod.perm is None else mod.perm.numel(), int_groups=mod.int_groups)
-    if pid is not None:
-        _ACT_CACHE.update(key=key, x=xin, a=a)
+    if pid is not None and (share is None or share > 1):
+        with _ACT_LOCK:
+            _ACT_CACHE["entries"][slot] = {"x": x_orig, "xin": xin, "sig": sig, "a": a,
+                                           "left": None if share is None else share - 1}
     return a
+
+
+def _validate_columns(idx, K, what):
+    """A column list installed into a layer (permutation, salient set) must hold distinct ids in [0, K): the
+    quantiser kernels turn it into 16-bit shared-memory offsets without a bounds check.  Offline / parity-replay
+    paths only (one device sync)."""
+    if idx is None or idx.numel() == 0:
+        return
+    i64 = torch.as_tensor(idx).long()
+    lo, hi = int(i64.min()), int(i64.max())
+    if lo < 0 or hi >= K:
+        raise ValueError(f"{what}: column ids must lie in [0, {K}), got [{lo}, {hi}]")
+    if int(torch.unique(i64).numel()) != i64.numel():
+        raise ValueError(f"{what}: duplicate column ids")
 
 
 def _check_choice(value, allowed, what):
@@ -267,12 +316,19 @@ class W4A4Linear(nn.Module):
             x2 = x
         else:
             raise ValueError(f"Unsupported input shape: {shape}")       # fake_quant.py:287
+        if act_perm is not None or out_perm is not None:               # parity replay of a recorded permutation
+            _validate_columns(act_perm, self.in_features, "act_perm")
+            _validate_columns(out_perm, self.full_out_features, "out_perm")
         if self.mode == "fused":
-            y = self._forward_fused(x2)
+            y = self._forward_fused(x, x2)
         else:
-            y = self._forward_reference(x2, act_perm, out_perm)
+            y = self._forward_reference(x2, act_perm)
         if self.tp_world > 1 and self.tp_gather_output:
             y = parallel.gather_columns(y, self.full_out_features, self.tp_group)
+        if self.output_quant_name != "None":                           # fake_quant.py:309-316, on the full width
+            y = self._quantize_output(y, out_perm)
+        if y.dtype != x2.dtype:
+            y = y.to(x2.dtype)
         return y.view(shape[0], shape[1], -1) if x.dim() == 3 else y
 
     # ---- column-parallel sharding over out_features; no reference counterpart
@@ -283,9 +339,9 @@ class W4A4Linear(nn.Module):
         without it the layer returns its [M, N_local] column block (consumer is column-local)."""
         if self.tp_world != 1:
             raise RuntimeError("layer is already sharded")
-        if self.output_quant_name != "None":
-            raise ValueError("column-parallel sharding of an output-quantised layer is not supported: the output "
-                             "quantiser groups columns across the whole width (fake_quant.py:309-316)")
+        if self.output_quant_name != "None" and not gather_output:
+            raise ValueError("an output-quantised layer must gather its output: the output quantiser groups columns "
+                             "across the whole width (fake_quant.py:309-316)")
         N = self.out_features
         lo, hi = parallel.shard_range(N, world, rank)
         if hi <= lo:
@@ -304,21 +360,18 @@ class W4A4Linear(nn.Module):
         self.tp_rank, self.tp_world, self.tp_group, self.tp_gather_output = rank, world, group, gather_output
         return self
 
-    def _forward_fused(self, x2):
+    def _forward_fused(self, x, x2):
         cdt = self.w_sal.dtype if self.w_sal is not None else (
             x2.dtype if x2.dtype in (torch.float16, torch.bfloat16) else torch.float16)
         xin = x2 if x2.dtype == cdt else x2.to(cdt)
         # layers fed by the same tensor with the same K partition (q/k/v, gate/up: same calibration statistics in
         # the reference, fake_quant.py:396-455) share one quantised activation
-        a = _shared_act(xin, self)
+        a = _shared_act(x, xin, self)
         w = ops.QuantizedRows(codes=self.w_codes, scales=self.w_scales, sal=self.w_sal, rows=self.out_features,
                               Kn=a.Kn, Ks=a.Ks, group_size=self.group_size, int_groups=a.int_groups)
-        y = ops.mixed_gemm(a, w, self.bias, out_dtype=cdt)
-        if self.output_quant_name != "None":
-            y = self._quantize_output(y)
-        return y if y.dtype == x2.dtype else y.to(x2.dtype)
+        return ops.mixed_gemm(a, w, self.bias, out_dtype=cdt)
 
-    def _forward_reference(self, x2, act_perm, out_perm):
+    def _forward_reference(self, x2, act_perm):
         q_x = self._fake_quant_nonsalient(x2, self.act_quant_name, act_perm)
         w = self._weight
         cdt = w.dtype if w.dtype in (torch.float16, torch.bfloat16) else torch.float16
@@ -326,11 +379,7 @@ class W4A4Linear(nn.Module):
         # F7) are cast to fp16 at the boundary -- stated tolerance in tests/DESIGN.md
         y = ops.mixed_gemm(None, None, self.bias, a_sal=q_x if q_x.dtype == cdt else q_x.to(cdt),
                            w_sal=w if w.dtype == cdt else self._weight16(cdt))
-        if y.dtype != x2.dtype:
-            y = y.to(x2.dtype)
-        if self.output_quant_name != "None":
-            y = self._quantize_output(y, out_perm)
-        return y
+        return y if y.dtype == x2.dtype else y.to(x2.dtype)        # the reference's y lives in x's dtype
 
     def _weight16(self, cdt):
         cache = getattr(self, "_w16_cache", None)
@@ -341,9 +390,9 @@ class W4A4Linear(nn.Module):
 
     def _quantize_output(self, y, out_perm=None):
         # fake_quant.py:309-316: the K-sized input mask indexes y's columns -> only valid when N == K
-        if self.salient_indices is not None and self.out_features != self.in_features:
+        if self.salient_indices is not None and self.full_out_features != self.in_features:
             raise IndexError(f"The shape of the mask [{self.in_features}] at index 0 does not match the shape of the "
-                             f"indexed tensor [{y.shape[0]}, {self.out_features}] at index 1")
+                             f"indexed tensor [{y.shape[0]}, {self.full_out_features}] at index 1")
         return self._fake_quant_nonsalient(y.contiguous(), self.output_quant_name, out_perm)
 
     # ---- offline weight path
@@ -364,9 +413,15 @@ class W4A4Linear(nn.Module):
         new._buffers["_weight"] = None
         new.weight_quant_name = weight_quant
         sal, keep = new._device_indices(w.device)
+        _validate_columns(weight_perm, module.in_features, "weight_perm")
         if mode == "fused":
             if weight_quant != "per_group" or act_quant != "per_group":
                 raise ValueError("mode='fused' needs weight_quant='per_group' and act_quant='per_group'")
+            qmax = 2 ** (quant_bits - 1) - 1
+            if not 2 <= quant_bits <= 8 or qmax * qmax * group_size >= 2 ** 22:
+                # the GEMM turns int32 group sums into floats with the 1.5 * 2^23 bias pattern: exact only below 2^22
+                raise ValueError(f"mode='fused' needs 2 <= quant_bits <= 8 and qmax^2 * group_size < 2^22 "
+                                 f"(quant_bits={quant_bits}, group_size={group_size})")
             new.int_fraction = int_fraction
             new._pack_fused(w, sort_key if sort_key is not None else importance)
         else:
@@ -399,6 +454,8 @@ class W4A4Linear(nn.Module):
         else:
             key = torch.as_tensor(key).to(device=dev, dtype=torch.float32)
             perm = ops.argsort_stable(key, subset=keep)
+        _validate_columns(perm, self.in_features, "permutation")      # NaN-free total order by construction; cheap
+        _validate_columns(sal, self.in_features, "salient_indices")
         cdt = w.dtype if w.dtype in (torch.float16, torch.bfloat16) else torch.float16
         G = (perm.numel() + self.group_size - 1) // self.group_size
         self.int_groups = _int_groups(G, self.group_size, self.int_fraction)
@@ -435,8 +492,9 @@ class W4A4Linear(nn.Module):
     def packed_bytes(self) -> int:
         """True storage of the layer (the reference's get_model_size stops counting quantised linears)."""
         if self.mode == "fused" and self.w_codes is not None:
-            Kn = self.perm.numel()      # at rest every quantised column is an int4 nibble + one 16-bit scale per group
-            n = self.out_features * ((Kn + 1) // 2) + self.out_features * ((Kn + self.group_size - 1) // self.group_size) * 2
+            Kn = self.perm.numel()      # at rest every quantised column is an int4 nibble (a byte when quant_bits > 4)
+            cb = (Kn + 1) // 2 if self.quant_bits <= 4 else Kn          # + one 16-bit scale per group
+            n = self.out_features * cb + self.out_features * ((Kn + self.group_size - 1) // self.group_size) * 2
             if self.w_sal is not None:
                 n += self.out_features * self.sal_sorted.numel() * self.w_sal.element_size()
             n += Kn * 4
@@ -466,8 +524,11 @@ class W4A4Linear(nn.Module):
             sc16 = self.w_scales.to(sdt)
             if not torch.equal(sc16.float(), self.w_scales):        # scales are values of the compute dtype
                 sc16 = self.w_scales
-            st.update(w_packed=cpu(ops.pack_int4(self.w_codes)), w_scales=cpu(sc16), w_sal=cpu(self.w_sal),
-                      perm=cpu(self.perm))
+            if self.quant_bits <= 4:        # nibbles hold [-8, 7]: wider codes are stored as bytes
+                st["w_packed"] = cpu(ops.pack_int4(self.w_codes))
+            else:
+                st["w_codes8"] = cpu(self.w_codes)
+            st.update(w_scales=cpu(sc16), w_sal=cpu(self.w_sal), perm=cpu(self.perm))
         else:
             st["weight"] = cpu(self._weight)
         return st
@@ -492,8 +553,16 @@ class W4A4Linear(nn.Module):
         put = lambda t: None if t is None else t.to(dev)
         new._buffers["bias"] = put(state["bias"])
         new._buffers["_weight"] = None
-        if "w_packed" in state:
-            new.w_codes = ops.unpack_int4(put(state["w_packed"]).contiguous())
+        K = meta["in_features"]
+        _validate_columns(state.get("perm"), K, "checkpoint permutation")
+        _validate_columns(state.get("salient_indices"), K, "checkpoint salient_indices")
+        if "w_packed" in state or "w_codes8" in state:
+            if "w_packed" in state:
+                if meta["quant_bits"] > 4:
+                    raise ValueError("checkpoint stores int4 nibbles but declares quant_bits > 4")
+                new.w_codes = ops.unpack_int4(put(state["w_packed"]).contiguous())
+            else:
+                new.w_codes = put(state["w_codes8"]).contiguous()
             new.w_scales = put(state["w_scales"]).float().contiguous()
             new.w_sal, new.perm = put(state["w_sal"]), put(state["perm"])
             new._set_partition_id()
@@ -534,6 +603,14 @@ def _swap(parent, attr, prefix, input_feat, guarded, quantize_output, kw, extra)
         int_fraction=extra.get("int_fraction"), **kw))
 
 
+def _mark_shared(parent, attrs):
+    """Layers of `attrs` that ended up with the same K partition share one quantised activation per forward."""
+    mods = [getattr(parent, a) for a in attrs]
+    for m in mods:
+        pid = getattr(m, "_partition_id", None)
+        m._share_n = 1 if pid is None else sum(getattr(o, "_partition_id", None) == pid for o in mods)
+
+
 def quantize_opt(model, weight_quant="per_tensor", act_quant="per_tensor", quantize_bmm_input=True, input_feat=None,
                  salient_prop=0, quant_bits=4, group_size=128, **extra):
     """fake_quant.py:377-461 -- OPT: fc1, fc2 per decoder layer; q/k/v (output-quantised when quantize_bmm_input)
@@ -546,10 +623,13 @@ def quantize_opt(model, weight_quant="per_tensor", act_quant="per_tensor", quant
         if isinstance(m, OPTDecoderLayer):
             for attr in ("fc1", "fc2"):
                 _swap(m, attr, prefix, input_feat, False, False, kw, extra)
+                _mark_shared(m, (attr,))
         elif isinstance(m, OPTAttention):
             for attr in ("q_proj", "k_proj", "v_proj"):
                 _swap(m, attr, prefix, input_feat, False, quantize_bmm_input, kw, extra)
             _swap(m, "out_proj", prefix, input_feat, False, False, kw, extra)
+            _mark_shared(m, ("q_proj", "k_proj", "v_proj"))
+            _mark_shared(m, ("out_proj",))
     return model
 
 
@@ -565,10 +645,14 @@ def quantize_llama_like(model, weight_quant="per_channel", act_quant="per_token"
         if isinstance(m, (LlamaMLP, MistralMLP)):
             for attr in ("gate_proj", "up_proj", "down_proj"):
                 _swap(m, attr, prefix, input_feat, True, False, kw, extra)
+            _mark_shared(m, ("gate_proj", "up_proj"))
+            _mark_shared(m, ("down_proj",))
         elif isinstance(m, (LlamaAttention, MistralAttention)):
             for attr in ("q_proj", "k_proj", "v_proj"):
                 _swap(m, attr, prefix, input_feat, True, quantize_bmm_input, kw, extra)
             _swap(m, "o_proj", prefix, input_feat, True, False, kw, extra)
+            _mark_shared(m, ("q_proj", "k_proj", "v_proj"))
+            _mark_shared(m, ("o_proj",))
     return model
 
 

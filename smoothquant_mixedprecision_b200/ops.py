@@ -192,7 +192,7 @@ def fakequant_rows(x: torch.Tensor, perm: Optional[torch.Tensor], group_size: in
     with torch.cuda.device(x.device):
         check(lib.mq_fakequant_rows(x2.data_ptr(), R, K, _ld(x2), _dtype_code(x2), _ptr(perm), Kn, int(group_size),
                                     n_bits, out.data_ptr(), _ld(out), _stream(x)), "mq_fakequant_rows")
-    if inplace:
+    if inplace and not x.is_inference():
         torch.autograd.graph.increment_version(x)      # written through a raw pointer: tell torch (and the act cache)
     return x if inplace else out.view(x.shape)
 
@@ -208,7 +208,7 @@ def fakequant_tensor(x: torch.Tensor, n_bits: int = 4, inplace: bool = False) ->
     with torch.cuda.device(x.device):
         check(lib.mq_fakequant_tensor(xc.data_ptr(), xc.numel(), _dtype_code(xc), n_bits, out.data_ptr(),
                                       ws.data_ptr(), 16, _stream(x)), "mq_fakequant_tensor")
-    if inplace:
+    if inplace and not x.is_inference():
         torch.autograd.graph.increment_version(x)
     return x if inplace else out.view(x.shape)
 
@@ -289,5 +289,11 @@ def mixed_gemm(a: Optional[QuantizedRows], w: Optional[QuantizedRows], bias: Opt
             torch.cuda.current_stream(dev).cuda_stream), "mq_mixed_gemm")
     if ev is not None:
         ev[1].record(torch.cuda.current_stream(dev))
-        GEMM_EVENTS.append((ev[0], ev[1], 2.0 * M * N * G * g, 2.0 * M * N * Ks))
+        # algorithmic work: the true quantised columns (zero padding of the last group is not work) on the integer
+        # pipe, the salient columns (+ hybrid tail) on the 16-bit pipe
+        kn_int = min(a.Kn, G * g) if a is not None else 0
+        ks_true = (a.n_salient if a is not None and a.n_salient is not None else Ks)
+        if a is not None and G * g < a.Kn:
+            ks_true += a.Kn - G * g
+        GEMM_EVENTS.append((ev[0], ev[1], 2.0 * M * N * kn_int, 2.0 * M * N * ks_true))
     return y[:, :N]

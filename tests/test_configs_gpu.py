@@ -1,0 +1,372 @@
+"""Every BASELINE.json config under `pytest -m gpu`, against the CPU oracle ("Next round" item 1).
+
+  config 1  OPT-125m at its real shape (hidden 768, ffn 3072, 12 layers, seq 512), g = 128, 5 % salient, max sort:
+            whole-model logits AND every one of the 72 swapped linears teacher-forced with the oracle model's own
+            inputs, in mode="reference" (literal layer) and mode="fused" (static partition).
+  config 2  OPT-1.3B layer shapes (K = 2048 / 8192, M = 2048), g = 64, 10 % salient, mean+3*STD key, both engines.
+  config 3  one Llama-2-7B decoder layer (hidden 4096, inter 11008, 32 heads), smooth alpha = 0.85 -> fused:
+            sampled tokens x sampled output columns of all 7 linears, and the whole layer's logits.
+  config 4/5  sampled sweep M in {1 .. 32768} x 7B/13B/70B linear shapes x g in {64, 128, 1024} x p in {0, 5, 10 %}.
+
+The oracle runs on the host CPU of the GPU box (tests/oracle_modules.py wraps oracle/mq_oracle.py as nn.Modules).
+Integer results (permutation, codes, scales, output-quantiser values given the same input) are compared bit for bit;
+floating-point results within the tolerance written next to each assertion.  Measured errors are appended to
+gpurun_out/parity_log.jsonl when that directory exists.
+"""
+import copy
+import json
+import os
+
+import pytest
+import torch
+from torch import nn
+
+import oracle_modules as OM
+from oracle import mq_oracle as O
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _log(**kv):
+    d = os.path.join(ROOT, "gpurun_out")
+    if os.path.isdir(d):
+        with open(os.path.join(d, "parity_log.jsonl"), "a") as f:
+            f.write(json.dumps(kv) + "\n")
+
+
+@pytest.fixture(scope="module")
+def fq():
+    from smoothquant_mixedprecision_b200 import fake_quant
+    return fake_quant
+
+
+@pytest.fixture(scope="module")
+def ops():
+    from smoothquant_mixedprecision_b200 import ops as _ops
+    return _ops
+
+
+def synth_gpu(M, K, seed):
+    """SURVEY 8(d) config 4 recipe: randn * lognormal(0, 0.5) per channel, 1 % of the channels x U(10, 40)."""
+    g = torch.Generator(device=DEV).manual_seed(seed)
+    c = torch.exp(0.5 * torch.randn(K, device=DEV, generator=g))
+    idx = torch.randperm(K, device=DEV, generator=g)[: max(1, K // 100)]
+    c[idx] *= torch.empty(idx.numel(), device=DEV).uniform_(10, 40, generator=g)
+    x = torch.randn(M, K, device=DEV, generator=g)
+    return x.mul_(c).half()
+
+
+def _sample(n, k, seed):
+    if n <= k:
+        return torch.arange(n)
+    g = torch.Generator().manual_seed(seed)
+    return torch.sort(torch.randperm(n, generator=g)[:k]).values
+
+
+def _check_fused_layer_sampled(fq, ops, mod, x, w_cpu, bias_cpu, imp, key, g, p, rows, cols, tag, tol_rel=1e-3):
+    """mod(x) on the GPU vs the composed oracle on sampled token rows x sampled output channels; packed weight codes /
+    scales, activation codes / scales and the permutation bit for bit on the same samples."""
+    K = x.shape[-1]
+    part = O.fused_partition(K, O.select_salient(imp, p) if p > 0 else None, key, g)
+    assert torch.equal(mod.perm.cpu().long(), part.perm)
+    xr = x[rows.to(DEV)].cpu()
+    y64, aq, wq = O.fused_layer_oracle(xr, w_cpu[cols], None if bias_cpu is None else bias_cpu[cols], part)
+    G, Gi = aq.scales.shape[1], mod.int_groups
+    # weights: integer groups as codes + scales, hybrid tail (if any) as the reference's dequantised value
+    assert torch.equal(mod.w_codes[cols.to(DEV)].cpu()[:, : Gi * g], wq.codes[:, : Gi * g])
+    assert torch.equal(mod.w_scales[:Gi].cpu()[:, cols].t(), wq.scales.float()[:, :Gi])
+    ks = part.salient.numel()
+    if Gi < G:
+        t0 = (ks + 7) // 8 * 8
+        assert torch.equal(mod.w_sal[cols.to(DEV)].cpu()[:, t0: t0 + wq.deq.shape[1] - Gi * g], wq.deq[:, Gi * g:])
+    # activations through K1 as the layer runs it
+    a = ops.quant_rows(x, mod.perm, mod.sal_sorted, g, 4, Kn=mod.perm.numel(), int_groups=Gi)
+    assert torch.equal(a.codes[rows.to(DEV)].cpu()[:, : Gi * g], aq.codes[:, : Gi * g])
+    assert torch.equal(a.scales[:Gi].cpu()[:, rows].t(), aq.scales.float()[:, :Gi])
+    if ks:
+        assert torch.equal(a.sal[rows.to(DEV)].cpu()[:, :ks], xr[:, part.salient])
+    y = mod(x)
+    assert y.shape == (x.shape[0], mod.out_features)
+    got = y[rows.to(DEV)][:, cols.to(DEV)].double().cpu()
+    err = float((got - y64).abs().max())
+    tol = tol_rel * float(y64.abs().max()) + 1e-3          # fp16 output rounding + fp32 accumulation order
+    _log(test=tag, err=err, tol=tol, ymax=float(y64.abs().max()))
+    assert err <= tol, (tag, err, tol)
+
+
+# ------------------------------------------------------------------------------------------------ configs 4 / 5
+SHAPES45 = [(11008, 4096), (4096, 11008), (13824, 5120), (1024, 8192), (28672, 8192), (8192, 28672)]   # (N, K)
+MS45 = [1, 8, 16, 64, 256, 4096, 32768]
+GP45 = [(64, 0.0), (128, 0.05), (1024, 0.10), (64, 0.05), (128, 0.10), (1024, 0.0), (64, 0.10), (128, 0.0),
+        (1024, 0.05)]
+POINTS45 = [(M, N, K) + GP45[(i * 7 + j) % 9] for i, (N, K) in enumerate(SHAPES45) for j, M in enumerate(MS45)]
+
+
+@pytest.mark.parametrize("M,N,K,g,p", POINTS45)
+def test_config45_gemm_sweep_sampled(fq, ops, M, N, K, g, p):
+    """All groups on the integer engine (int_fraction = 1.0, also for g = 64), the packed weight and the activation
+    codes torch.equal with oracle.group_quant on the sampled rows, y within 1e-3 * max|y| + 1e-3 of the fp64
+    composition of the oracle's codes and scales (fake_quant.py:280-322 under the static partition)."""
+    seed = M * 7 + N + K + g
+    x = synth_gpu(M, K, seed)
+    imp = x.abs().float().mean(dim=0).cpu()
+    key = x.abs().amax(dim=0).float().cpu()
+    torch.manual_seed(seed)
+    lin = nn.Linear(K, N, bias=(N // 8) % 2 == 0, device=DEV, dtype=torch.float16)
+    with torch.no_grad():
+        lin.weight.copy_(torch.randn(N, K, device=DEV) * 0.02)
+    mod = fq.W4A4Linear.from_float(lin, "per_group", "per_group", importance=imp if p > 0 else None, salient_prop=p,
+                                   group_size=g, mode="fused", sort_key=key, int_fraction=1.0)
+    rows, cols = _sample(M, 64, seed), _sample(N, 96, seed + 1)
+    w_cpu = lin.weight.data[cols.to(DEV)].cpu()
+    bias_cpu = None if lin.bias is None else lin.bias.data[cols.to(DEV)].cpu()
+    # the oracle sees only the sampled output channels: index them 0..n-1
+    _check_fused_layer_sampled(fq, ops, _ColView(mod, cols), x, w_cpu, bias_cpu, imp, key, g, p, rows,
+                               torch.arange(cols.numel()), f"cfg45 M={M} N={N} K={K} g={g} p={p}")
+    del mod, lin, x
+    fq.clear_act_cache()
+
+
+class _ColView:
+    """The sampled output channels of a packed layer, presented with the attributes _check_fused_layer_sampled reads
+    (so that only those weight rows travel to the CPU oracle)."""
+
+    def __init__(self, mod, cols):
+        c = cols.to(DEV)
+        self.mod, self.c = mod, c
+        self.perm, self.sal_sorted, self.int_groups = mod.perm, mod.sal_sorted, mod.int_groups
+        self.w_codes = mod.w_codes[c]
+        self.w_scales = mod.w_scales[:, c]
+        self.w_sal = None if mod.w_sal is None else mod.w_sal[c]
+        self.out_features = c.numel()
+
+    def __call__(self, x):
+        return self.mod(x)[:, self.c]
+
+
+# ------------------------------------------------------------------------------------------------ config 2
+@pytest.mark.parametrize("N,K", [(2048, 2048), (8192, 2048), (2048, 8192)])
+@pytest.mark.parametrize("int_fraction", [1.0, None])
+def test_config2_opt13b_layer_shapes(fq, ops, N, K, int_fraction):
+    """OPT-1.3B linears, prefill 2048 tokens, g = 64, 10 % salient, mean+3*STD sort key (README.md:36; parity of the
+    KEY is unpinned, SURVEY F2 -- the key the GPU computes is handed to the oracle, and checked against the oracle's
+    own statistic to 2e-4).  int_fraction 1.0 = integer engine, None = the default for g < 128."""
+    M, g, p = 2048, 64, 0.10
+    x = synth_gpu(M, K, 1300 + N + K)
+    imp = x.abs().float().mean(dim=0).cpu()
+    key = ops.colstat(x, "mean3std").cpu()
+    assert torch.allclose(key, O.sort_key(x.cpu(), "mean3std"), rtol=2e-4, atol=1e-6)
+    torch.manual_seed(N + K)
+    lin = nn.Linear(K, N, bias=True, device=DEV, dtype=torch.float16)
+    with torch.no_grad():
+        lin.weight.copy_(torch.randn(N, K, device=DEV) * 0.02)
+    mod = fq.W4A4Linear.from_float(lin, "per_group", "per_group", importance=imp, salient_prop=p, group_size=g,
+                                   mode="fused", sort="mean3std", sort_key=key, int_fraction=int_fraction)
+    rows, cols = _sample(M, 128, 5), _sample(N, 256, 6)
+    _check_fused_layer_sampled(fq, ops, _ColView(mod, cols), x, lin.weight.data[cols.to(DEV)].cpu(),
+                               lin.bias.data[cols.to(DEV)].cpu(), imp, key, g, p, rows, torch.arange(cols.numel()),
+                               f"cfg2 N={N} K={K} int_fraction={int_fraction}")
+    fq.clear_act_cache()
+
+
+# ------------------------------------------------------------------------------------------------ config 1
+def _opt125m(seed):
+    from transformers import OPTConfig, OPTForCausalLM
+    torch.manual_seed(seed)
+    cfg = OPTConfig(vocab_size=50272, hidden_size=768, ffn_dim=3072, num_hidden_layers=12, num_attention_heads=12,
+                    max_position_embeddings=2048, word_embed_proj_dim=768)
+    return OPTForCausalLM(cfg).eval()
+
+
+@pytest.fixture(scope="module")
+def opt125m_case():
+    model = _opt125m(125)
+    g = torch.Generator().manual_seed(1)
+    calib = [torch.randint(0, 50272, (1, 512), generator=g) for _ in range(2)]
+    ids = torch.randint(0, 50272, (1, 512), generator=g)
+    feat = OM.hook_input_feat(model, calib)                    # run_experiments.py:55-84 on synthetic token blocks
+    return {"state": copy.deepcopy(model.state_dict()), "feat": feat, "ids": ids}
+
+
+def _teacher_forced(fq, gpu_model, rec, mode, tag):
+    """Every swapped linear of the GPU model on the oracle model's own input: y before the output quantiser within the
+    fp16 tolerance of the mode, and the output quantiser (K3, fake_quant.py:309-316) bit-exact on the GPU's own y."""
+    worst = 0.0
+    for name, (xin, yref) in rec.items():
+        mod = gpu_model.get_submodule(name)
+        assert isinstance(mod, fq.W4A4Linear), name
+        oq, mod.output_quant_name = mod.output_quant_name, "None"
+        y_pre = mod(xin.to(DEV)).cpu()
+        mod.output_quant_name = oq
+        ref_pre = yref["pre"].float()
+        # reference mode: fp32 fake-quant values enter the GEMM as fp16 (4e-3 like tests/test_layer_gpu.py);
+        # fused mode: exact integer arithmetic, fp16 output rounding only
+        rel = 4e-3 if mode == "reference" else 1e-3
+        err = float((y_pre.float() - ref_pre).abs().max())
+        tol = rel * float(ref_pre.abs().max()) + 1e-3
+        worst = max(worst, err / tol)
+        assert err <= tol, (name, err, tol)
+        if oq != "None":
+            sal = mod.salient_indices
+            # fused mode quantises y in the 16-bit compute dtype, reference mode in the module's own dtype
+            yq = y_pre.to(mod.w_sal.dtype) if mode == "fused" else y_pre
+            want = OM.output_quant_oracle(yq.reshape(-1, yq.shape[-1]), sal, mod.group_size).view(y_pre.shape)
+            got = mod(xin.to(DEV)).cpu()
+            assert torch.equal(got, want.to(got.dtype)), name
+    _log(test=tag, worst_err_over_tol=worst, layers=len(rec))
+
+
+class _PreQuantTap:
+    """Record (input, {pre: y before the output quantiser, out: y}) of every oracle-backed linear."""
+
+    def __init__(self, model):
+        self.rec, self.hooks = {}, []
+        for name, m in model.named_modules():
+            if isinstance(m, (OM.OracleRefLinear, OM.OracleFusedLinear)):
+                self.hooks.append(m.register_forward_hook(lambda m, x, y, name=name: self._hook(m, x, y, name)))
+
+    def _hook(self, m, x, y, name):
+        x = x[0] if isinstance(x, tuple) else x
+        if isinstance(m, OM.OracleFusedLinear):     # unrounded, so that the comparison sees one fp16 rounding only
+            pre = m.pre_quant_f32(x.reshape(-1, x.shape[-1])).view(*x.shape[:-1], -1)
+        else:
+            pre = m.forward(x, quantize_output=False) if m.qo else y
+        self.rec[name] = (x.detach().clone(), {"pre": pre.detach().clone(), "out": y.detach().clone()})
+
+    def remove(self):
+        for h in self.hooks:
+            h.remove()
+
+
+@pytest.mark.parametrize("mode", ["reference", "fused"])
+def test_config1_opt125m_real_shape(fq, opt125m_case, mode):
+    c = opt125m_case
+    cpu = _opt125m(0)
+    cpu.load_state_dict(c["state"])
+    OM.oracle_swap(cpu, "opt", mode, c["feat"], 0.05, 128)
+    tap = _PreQuantTap(cpu)
+    with torch.no_grad():
+        ref = cpu(c["ids"]).logits.float()
+    tap.remove()
+    assert len(tap.rec) == 72
+    gpu = _opt125m(0)
+    gpu.load_state_dict(c["state"])
+    gpu = gpu.to(DEV)
+    fq.quantize_opt(gpu, "per_group", "per_group", input_feat=c["feat"], salient_prop=0.05, group_size=128, mode=mode)
+    n = sum(isinstance(m, fq.W4A4Linear) for m in gpu.modules())
+    assert n == 72 and not isinstance(gpu.lm_head, fq.W4A4Linear)
+    if mode == "reference":       # literal weights: bit-exact against the oracle's a3 + salient restore
+        for name, m in cpu.named_modules():
+            if isinstance(m, OM.OracleRefLinear):
+                assert torch.equal(gpu.get_submodule(name).weight.cpu(), m.weight_q), name
+    _teacher_forced(fq, gpu, tap.rec, mode, f"cfg1 opt125m {mode} teacher-forced")
+    with torch.no_grad():
+        logits = gpu(c["ids"].to(DEV)).logits.float().cpu()
+    rel = float((logits - ref).norm() / ref.norm())
+    ok, sure = OM.margin_top1_agree(logits, ref)
+    _log(test=f"cfg1 opt125m {mode} logits", rel_l2=rel, top1_sure=sure, top1_ok=ok,
+         top1_raw=float((logits.argmax(-1) == ref.argmax(-1)).float().mean()))
+    # free-running logits: 12 layers of 4-bit re-quantisation (q/k/v outputs) amplify GEMM-rounding differences into
+    # whole quantisation steps, so the bound is a noise-level one; the per-layer bound above is the tight one
+    assert rel < 0.15, rel
+    assert ok
+    fq.clear_act_cache()
+
+
+@pytest.mark.parametrize("kind", ["llama", "opt"])
+def test_tiny_models_fused_mode_logits(fq, golden_models, kind):
+    """mode="fused" at model level (the path bench.py times) against the oracle-backed fused model."""
+    from test_layer_gpu import _build
+    c = golden_models[kind]
+    cpu = _build(kind, c["config"])
+    cpu.load_state_dict(c["state_smoothed"])
+    OM.oracle_swap(cpu, kind, "fused", c["input_feat"], c["salient_prop"], c["group_size"])
+    tap = _PreQuantTap(cpu)
+    with torch.no_grad():
+        ref = cpu(c["ids"]).logits.float()
+    tap.remove()
+    gpu = _build(kind, c["config"])
+    gpu.load_state_dict(c["state_smoothed"])
+    gpu = gpu.to(DEV)
+    walker = fq.quantize_model if kind == "llama" else fq.quantize_opt
+    walker(gpu, weight_quant="per_group", act_quant="per_group", input_feat=c["input_feat"],
+           salient_prop=c["salient_prop"], group_size=c["group_size"], mode="fused")
+    _teacher_forced(fq, gpu, tap.rec, "fused", f"tiny {kind} fused teacher-forced")
+    with torch.no_grad():
+        logits = gpu(c["ids"].to(DEV)).logits.float().cpu()
+    rel = float((logits - ref).norm() / ref.norm())
+    ok, sure = OM.margin_top1_agree(logits, ref)
+    _log(test=f"tiny {kind} fused logits", rel_l2=rel, top1_sure=sure, top1_ok=ok)
+    assert rel < (0.15 if kind == "opt" else 2e-2), rel
+    assert ok
+    fq.clear_act_cache()
+
+
+# ------------------------------------------------------------------------------------------------ config 3
+def test_config3_llama7b_decoder_layer(fq, ops):
+    """One decoder layer at Llama-2-7B shape: smooth_lm(alpha = 0.85) (smooth.py:126-141) -> quantize_llama_like in
+    mode="fused" (fake_quant.py:464-561), g = 128, 5 % salient.  (1) the smoothing is bit-identical to the oracle's
+    formula; (2) all 7 linears on 2 x 2048 tokens: 256 sampled tokens x 256 sampled output channels against the composed
+    oracle, weight codes bit-exact; (3) the layer's logits on 256 tokens against the oracle-backed layer on the CPU."""
+    from transformers import LlamaConfig, LlamaForCausalLM
+    from smoothquant_mixedprecision_b200.smooth import smooth_lm
+    torch.manual_seed(7)
+    cfg = LlamaConfig(vocab_size=512, hidden_size=4096, intermediate_size=11008, num_hidden_layers=1,
+                      num_attention_heads=32, num_key_value_heads=32, max_position_embeddings=2048)
+    cpu = LlamaForCausalLM(cfg).half().eval()
+    gen = torch.Generator().manual_seed(3)
+    calib = [torch.randint(0, 512, (1, 512), generator=gen).to(DEV) for _ in range(2)]
+    ids = torch.randint(0, 512, (2, 2048), generator=gen)
+    gpu = copy.deepcopy(cpu).to(DEV)
+    act_scales = OM.hook_act_scales(gpu, calib)
+    lay = cpu.model.layers[0]
+    qkv0 = [m.weight.data.clone() for m in (lay.self_attn.q_proj, lay.self_attn.k_proj, lay.self_attn.v_proj)]
+    ln0 = lay.input_layernorm.weight.data.clone()
+    smooth_lm(cpu, act_scales, 0.85)                           # CPU: pure weight transform
+    s = O.smooth_scales(act_scales["model.layers.0.self_attn.q_proj"], qkv0, 0.85)
+    assert torch.equal(lay.input_layernorm.weight.data, ln0 / s)
+    assert torch.equal(lay.self_attn.q_proj.weight.data, qkv0[0] * s.view(1, -1))
+    gpu.load_state_dict(cpu.state_dict())
+    feat = OM.hook_input_feat(gpu, calib)
+    fq.quantize_llama_like(gpu, "per_group", "per_group", input_feat=feat, salient_prop=0.05, group_size=128,
+                           mode="fused")
+    rec, remove = OM.capture_io(gpu, fq.W4A4Linear)
+    with torch.no_grad():
+        gpu(ids.to(DEV))
+    remove()
+    assert len(rec) == 7
+    worst = 0.0
+    for name, (xin, yout) in rec.items():
+        mod = gpu.get_submodule(name)
+        lin = cpu.get_submodule(name)
+        x2 = xin.reshape(-1, xin.shape[-1])
+        y2 = yout.reshape(-1, yout.shape[-1])
+        rows, cols = _sample(x2.shape[0], 256, 11), _sample(mod.out_features, 256, 12)
+        imp = sum(feat[name]).float()
+        part = O.fused_partition(mod.in_features, O.select_salient(imp, 0.05), imp, 128)
+        assert torch.equal(mod.perm.cpu().long(), part.perm), name
+        y64, aq, wq = O.fused_layer_oracle(x2[rows.to(DEV)].cpu(), lin.weight.data[cols], None, part)
+        G = aq.scales.shape[1]
+        assert mod.int_groups == G
+        assert torch.equal(mod.w_codes[cols.to(DEV)].cpu()[:, : G * 128], wq.codes), name
+        assert torch.equal(mod.w_scales[:, cols.to(DEV)].cpu().t(), wq.scales.float()), name
+        got = y2[rows.to(DEV)][:, cols.to(DEV)].double().cpu()
+        err, tol = float((got - y64).abs().max()), 1e-3 * float(y64.abs().max()) + 1e-3
+        worst = max(worst, err / tol)
+        assert err <= tol, (name, err, tol)
+    _log(test="cfg3 llama7b layer sampled linears", worst_err_over_tol=worst)
+    # whole layer, free running, on 256 tokens
+    OM.oracle_swap(cpu, "llama", "fused", feat, 0.05, 128)
+    cpu = cpu.float()                                          # attention / norms in fp32 on the CPU; the oracle
+    ids1 = ids[:1, :256]                                       # modules cast to fp16 at their boundary themselves
+    with torch.no_grad():
+        ref = cpu(ids1).logits.float()
+        logits = gpu(ids1.to(DEV)).logits.float().cpu()
+    rel = float((logits - ref).norm() / ref.norm())
+    ok, sure = OM.margin_top1_agree(logits, ref)
+    _log(test="cfg3 llama7b layer logits", rel_l2=rel, top1_sure=sure, top1_ok=ok)
+    assert rel < 5e-2, rel          # fp16 attention / norm on the GPU vs fp32 on the CPU, one layer of 4-bit quantisers
+    assert ok
+    fq.clear_act_cache()

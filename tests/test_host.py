@@ -50,6 +50,32 @@ def test_drop_in_import_paths():
     from smoothquant.smooth import smooth_lm as s2                       # ppl_eval.py:4
     assert smooth_lm is s2 and callable(quantize_model) and smoothquant.__all__ == ["smooth_lm", "quantize_model"]
     assert W4A4Linear.__name__ == "W4A4Linear" and callable(quantize_llama_like) and callable(quantize_opt)
+    from smoothquant.model_size import get_model_size                    # run_experiments.py:22
+    import inspect
+    assert [p.name for p in inspect.signature(get_model_size).parameters.values()] == \
+        ["model", "data_width", "salient_prop", "group_size"]            # smoothquant/model_size.py:5
+
+
+def test_model_size_matches_reference_formula_on_float_models():
+    """smoothquant/model_size.py:5-15 on a model without swapped linears (bits, not bytes)."""
+    from smoothquant.model_size import get_model_size
+    m = torch.nn.Sequential(torch.nn.Linear(64, 32), torch.nn.Linear(32, 8, bias=False))
+    n = 64 * 32 + 32 + 32 * 8
+    assert get_model_size(m) == n * 16
+    assert get_model_size(m, data_width=4, group_size=128) == n * (4 + 20 / 128)
+    assert get_model_size(m, data_width=4, salient_prop=0.05, group_size=64) == \
+        n * ((4 + 20 / 64) * 0.95 + (16 + 20 / 64) * 0.05)
+
+
+def test_column_list_validation():
+    """a permutation / salient list with out-of-range or duplicate ids must be rejected before it reaches
+    the kernels (they turn it into unchecked 16-bit shared-memory offsets)."""
+    from smoothquant_mixedprecision_b200.fake_quant import _validate_columns
+    _validate_columns(torch.tensor([3, 0, 2]), 4, "ok")
+    _validate_columns(None, 4, "none")
+    for bad in ([0, 4], [-1, 2], [1, 1, 2]):
+        with pytest.raises(ValueError):
+            _validate_columns(torch.tensor(bad), 4, "perm")
 
 
 def test_no_cpu_fallback_and_python_side_errors():

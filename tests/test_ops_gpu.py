@@ -61,6 +61,16 @@ def test_argsort_stable(ops, n):
         assert torch.equal(got, want)
 
 
+def test_argsort_orders_nan_and_inf_keys_like_torch(ops):
+    """NaN keys compare false with everything; the rank must still be a total order (NaN above +inf,
+    ties by index) so that the output is a permutation."""
+    key = torch.tensor([1.0, float("nan"), -2.0, float("inf"), float("nan"), -float("inf"), 1.0, 0.0])
+    for desc in (False, True):
+        got = ops.argsort_stable(key.to(DEV), descending=desc).cpu().long()
+        assert sorted(got.tolist()) == list(range(8))
+        assert torch.equal(got, torch.argsort(key, stable=True, descending=desc))
+
+
 # ------------------------------------------------------------------------------------------------ K1 / P0
 def _check_quant_rows(ops, x, g, n_bits, perm, sal, smooth=None):
     xs = x if smooth is None else (x / smooth)
