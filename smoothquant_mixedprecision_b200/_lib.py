@@ -9,7 +9,8 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libmq.so")
+# MQ_LIB: an alternative build of the same library (kernel-variant experiments, tools/build_variant.sh); no fallback
+LIB_PATH = os.environ.get("MQ_LIB") or os.path.join(HERE, "libmq.so")
 
 MQ_F16, MQ_BF16, MQ_F32 = 0, 1, 2
 MQ_STAT_ABSMAX, MQ_STAT_ABSMEAN, MQ_STAT_MEAN3STD, MQ_STAT_ARGMAX = 0, 1, 2, 3

@@ -18,8 +18,8 @@ CSRC = os.path.join(HERE, "csrc")
 BUILD = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "libmq.so")
 SOURCES = ["common.cu", "colstat.cu", "quant_rows.cu", "mixed_gemm.cu"]
-HEADERS = [os.path.join(CSRC, "common.cuh"), os.path.join(CSRC, "ptx.cuh"),
-           os.path.join(os.path.dirname(HERE), "include", "mq.h")]
+HEADERS = sorted(os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith(".cuh")) + \
+    [os.path.join(os.path.dirname(HERE), "include", "mq.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr", "-Wno-deprecated-gpu-targets"]
 

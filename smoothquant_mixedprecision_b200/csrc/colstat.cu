@@ -183,21 +183,24 @@ int dispatch_kind(int kind, const void* x, int64_t M, int64_t K, int64_t ld, flo
 constexpr int kSortTile = 2048;
 
 // total order on the keys: NaN compares false with everything, which would give every NaN key the same rank and
-// leave output slots unwritten.  NaN is ordered like torch.argsort orders it -- above +inf (last when ascending,
-// first when descending) -- by mapping it to +inf before the optional negation; ties fall back to the index.
-__device__ __forceinline__ float sort_canon(float k, int descending) {
-  if (k != k) k = __int_as_float(0x7f800000);
-  return descending ? -k : k;
+// leave output slots unwritten.  Keys are compared through the usual order-preserving map float -> uint32 with NaN
+// canonicalised to the positive quiet NaN (above +inf, where torch.argsort puts it) and -0 to +0 (equal keys tie by
+// index); descending order is the complement.
+__device__ __forceinline__ uint32_t sort_canon(float k, int descending) {
+  k += 0.0f;
+  uint32_t u = (k != k) ? 0x7fc00000u : __float_as_uint(k);
+  u = (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+  return descending ? ~u : u;
 }
 
 __global__ void __launch_bounds__(256)
 argsort_rank_kernel(const float* __restrict__ key, const int32_t* __restrict__ subset, int n, int descending,
                     int32_t* __restrict__ out) {
-  __shared__ float sk[kSortTile];
+  __shared__ uint32_t sk[kSortTile];
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   const bool live = i < n;
   int id = 0;
-  float ki = 0.f;
+  uint32_t ki = 0u;
   if (live) {
     id = subset ? subset[i] : i;
     ki = sort_canon(key[id], descending);

@@ -51,7 +51,22 @@ constexpr int kAllocWarp = kEpiWarps + 2;
 // + one idle warp: setmaxnreg is a warpgroup-wide instruction, so the issue warps must form a complete group of 4
 // (an 11-warp CTA hung on the B200)
 constexpr int kThreads = (kEpiWarps + 4) * 32;
-constexpr int kEpiRegs = kEpiWarps == 8 ? 232 : 104;  // 16: ptxas launches 608 threads with 96 registers -> 104 after the issue warps shrink to 40
+#ifndef MQ_GEMM_EPI_REGS
+// 8 epilogue warps: 384 threads launch with 168 registers = 64 512; 8 x 32 x 240 + 4 x 32 x 24 = 64 512 as well, so the
+// epilogue gets 240 registers when the four issue warps shrink to the minimum of 24 (they spill nothing at 24).  240
+// is what lets the TMEM drain run as double-buffered x32 loads (64 registers of in-flight sums) without spills:
+// 0.588 -> 0.576 ms at 32768 x 4096 x 4096 (r02; single-buffered x32 / x64 at 232 registers spill and lose).
+// 16 epilogue warps: ptxas launches 608 threads with 96 registers -> 104 after the issue warps shrink to 40.
+#define MQ_GEMM_EPI_REGS (MQ_GEMM_EPI_WARPS == 8 ? 240 : 104)
+#endif
+#ifndef MQ_GEMM_ISSUE_REGS
+#define MQ_GEMM_ISSUE_REGS (MQ_GEMM_EPI_WARPS == 8 ? 24 : 40)
+#endif
+#ifndef MQ_GEMM_NBUF
+#define MQ_GEMM_NBUF 2   // TMEM drain chunks in flight per epilogue thread: 2 = load chunk c+1 while chunk c is rescaled, 1 = none
+#endif
+constexpr int kEpiRegs = MQ_GEMM_EPI_REGS;
+constexpr int kNBuf = MQ_GEMM_NBUF;
 static_assert(kEpiWarps == 8 || kEpiWarps == 16, "8 or 16 epilogue warps");
 
 struct GemmArgs {
@@ -95,7 +110,7 @@ constexpr int kMagicMmaMaxGroup = 256;
 #define MQ_GEMM_UNIFORM 2   // 0: plain thread-derived addresses (experiments), 1: uniform warp index, 2: + opaque uniform addresses
 #endif
 #ifndef MQ_GEMM_CH
-#define MQ_GEMM_CH 16
+#define MQ_GEMM_CH (MQ_GEMM_EPI_WARPS == 8 ? 32 : 16)
 #endif
 #ifndef MQ_GEMM_SCALE_ON_FULL
 #define MQ_GEMM_SCALE_ON_FULL 1
@@ -103,6 +118,10 @@ constexpr int kMagicMmaMaxGroup = 256;
 constexpr bool kScaleOnFull = MQ_GEMM_SCALE_ON_FULL != 0;
 __device__ __forceinline__ void tmem_ld_chunk(uint32_t taddr, uint32_t (&v)[16]) { tmem_ld_32x16(taddr, v); }
 __device__ __forceinline__ void tmem_ld_chunk(uint32_t taddr, uint32_t (&v)[32]) { tmem_ld_32x32(taddr, v); }
+__device__ __forceinline__ void tmem_ld_chunk(uint32_t taddr, uint32_t (&v)[64]) {   // two x32 loads, one wait
+  tmem_ld_32x32(taddr, *reinterpret_cast<uint32_t (*)[32]>(&v[0]));
+  tmem_ld_32x32(taddr + 32u, *reinterpret_cast<uint32_t (*)[32]>(&v[32]));
+}
 #ifndef MQ_GEMM_PAIR_DEFAULT
 #define MQ_GEMM_PAIR_DEFAULT 3  // 1: CTA-pair kernel whenever possible;  2: single-CTA kernel;  3: by tile count
 #endif
@@ -260,7 +279,7 @@ mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
 #endif
 
   if (warp >= kEpiWarps) {
-    reg_dealloc<40>();
+    reg_dealloc<MQ_GEMM_ISSUE_REGS>();
     // Producer and MMA issuer run as whole warps with warp-uniform control flow; the asynchronous instructions are
     // issued by one elected lane.  (A `lane == 0` branch around the whole loop makes ptxas treat every operand of
     // UTMALDG / UTCIMMA as potentially divergent and wrap each issue in a vote / R2UR waterfall.)
@@ -532,17 +551,18 @@ mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
         const float as = __uint_as_float(__float_as_uint(as_raw) & 0xFFFFFFFCu);
         const float cas = -kMagic * as;
         constexpr int CH = MQ_GEMM_CH;  // columns per TMEM load (double buffered: 2 x CH registers)
-        uint32_t v[2][CH];
+        uint32_t v[kNBuf][CH];
 #ifdef MQ_DEBUG_NOLDTM
         const bool dbg_nomath = kProf && (p.debug & 4), dbg_noload = true;
 #else
         const bool dbg_nomath = kProf && (p.debug & 4), dbg_noload = kProf && (p.debug & 8);
 #endif
-        if (!dbg_noload) tmem_ld_chunk(taddr, v[0]);
+        if (kNBuf == 2 && !dbg_noload) tmem_ld_chunk(taddr, v[0]);
 #pragma unroll
         for (int c = 0; c < CW / CH; ++c) {
+          if (kNBuf == 1 && !dbg_noload) tmem_ld_chunk(taddr + (uint32_t)(c * CH), v[0]);
           tmem_ld_wait();
-          if (c + 1 < CW / CH && !dbg_noload) tmem_ld_chunk(taddr + (uint32_t)((c + 1) * CH), v[(c + 1) & 1]);
+          if (kNBuf == 2 && c + 1 < CW / CH && !dbg_noload) tmem_ld_chunk(taddr + (uint32_t)((c + 1) * CH), v[(c + 1) & (kNBuf - 1)]);
           if (kRefill) {  // chunk c has been read: refill it
 #pragma unroll
             for (int r = 0; r < CH / 8; ++r) tmem_st_32x8(taddr + (uint32_t)(c * CH + r * 8), magic);
@@ -553,7 +573,7 @@ mixed_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
             __syncwarp();
             if (lane == 0) release_tmem(t);
           }
-          const uint32_t* vv = v[c & 1];
+          const uint32_t* vv = v[c & (kNBuf - 1)];
 #ifdef MQ_DEBUG_NOMATH
           acc[c].x += __uint_as_float(vv[0]) + __uint_as_float(vv[15]);
           continue;

@@ -291,7 +291,7 @@ def test_fused_forward_under_inference_mode(fq):
         h0 = fq._ACT_CACHE["hits"]
         got = [m(xi) for m in mods]
         assert fq._ACT_CACHE["hits"] == h0 + 1
-        ref = fq.W4A4Linear.from_float(lins[0], "per_token", "per_token")(xi.clone())   # in-place quantiser path
+        ref = fq.W4A4Linear.from_float(lins[0], "per_channel", "per_token")(xi.clone())   # in-place quantiser path
         assert ref.shape == (40, 256)
     assert all(torch.equal(a, b) for a, b in zip(got, want))
     fq.clear_act_cache()

@@ -121,6 +121,41 @@ def test_quant_rows_fast_path(ops, R, K, g, dtype):
         _check_quant_rows(ops, x, g, 4, order[ks:], torch.sort(order[:ks]).values, smooth=sm)
 
 
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("R,K,g,ks", [(130, 4096, 128, 204), (37, 11008, 128, 550), (64, 2048, 64, 204), (9, 1024, 32, 0),
+                                      (33, 2048, 1024, 100), (16, 8192, 256, 819), (5, 512, 128, 0)])
+def test_quant_rows_h2_contiguous_layout_and_kernel_agreement(ops, mqlib, R, K, g, ks, dtype):
+    """The packed-pair kernel (quant_rows_h2) in both of its modes against the oracle and against the r01 kernels:
+    gather mode (explicit permutation) and contiguous mode (perm=None: quantised columns first, salient tail behind,
+    the layout a folded producer emits), including magnitudes that drive scales into the fp16 denormal range (exact
+    fp32 fallback inside the kernel) and groups straddling Kn (zero padding, fake_quant.py:84-86)."""
+    x = synth(R, K, dtype, seed=R * 3 + K)
+    x[: R // 3] *= 1e-4                                     # tiny rows: denormal scales -> slow path
+    x[R // 3, : K // 2] = 0.0
+    Kn = K - ks
+    sal = torch.arange(Kn, K) if ks else None
+    want = O.group_quant(x[:, :Kn], 4, g)
+    G = want.scales.shape[1]
+    outs = {}
+    for h2 in (1, 2):
+        mqlib.set_option("quant_h2", h2)
+        try:
+            q = ops.quant_rows(x.to(DEV), None, None if sal is None else sal.to(DEV), g, 4, Kn=Kn)
+            qg = ops.quant_rows(x.to(DEV), torch.arange(Kn).to(DEV), None if sal is None else sal.to(DEV), g, 4)
+        finally:
+            mqlib.set_option("quant_h2", 0)
+        for name, r in (("contig", q), ("gather", qg)):
+            codes = r.codes.cpu()
+            assert torch.equal(codes[:, : G * g], want.codes), (name, h2)
+            assert int(codes[:, G * g:].abs().max()) == 0 if codes.shape[1] > G * g else True
+            assert torch.equal(r.scales.cpu()[:, :R].t(), want.scales.float()), (name, h2)
+            if ks:
+                assert torch.equal(r.sal.cpu()[:, :ks], x[:, Kn:]), (name, h2)
+                assert float(r.sal.cpu()[:, ks:].abs().sum()) == 0.0
+        outs[h2] = q
+    assert torch.equal(outs[1].codes, outs[2].codes) and torch.equal(outs[1].scales, outs[2].scales)
+
+
 def test_quant_rows_zero_rows_and_nbits8(ops):
     x = torch.zeros(8, 256, dtype=torch.float16)
     _check_quant_rows(ops, x, 128, 4, torch.arange(256), None)                 # all-zero groups: scale = fp16(1e-5)/7
