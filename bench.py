@@ -304,9 +304,14 @@ def build_stack(layers, tokens, dev, seed, tp=None):
             mods[name] = W4A4Linear.from_float(lin, "per_group", "per_group", importance=imp.cpu(),
                                                salient_prop=SALIENT, group_size=GROUP, mode="fused",
                                                sort_key=imp * 4.0)
-            if tp is not None:        # column-parallel: gather only where the consumer needs the full width
-                mods[name].shard_(tp[0], tp[1], gather_output=dict(PLAN)[name])
             del lin
+        # down_proj's static permutation folded into gate / up (SiLU * mul commutes with a channel permutation):
+        # its quantiser then reads contiguous vectors (fake_quant.fold_mlp_permutation)
+        from smoothquant_mixedprecision_b200.fake_quant import fold_mlp_permutation
+        fold_mlp_permutation(mods["gate_proj"], mods["up_proj"], mods["down_proj"])
+        if tp is not None:            # column-parallel: gather only where the consumer needs the full width
+            for name in mods:
+                mods[name].shard_(tp[0], tp[1], gather_output=dict(PLAN)[name])
         stack.append(mods)
     x0 = (torch.randn(tokens, HIDDEN, device=dev, generator=g) * chan[HIDDEN]).half()
     return stack, x0

@@ -37,7 +37,7 @@ __all__ = [
     "quantize_activation_per_token_absmax", "quantize_activation_per_tensor_absmax",
     "quantize_activation_per_group_absmax", "quantize_activation_per_group_absmax_sort",
     "quantize_weight_per_group_absmax_sort", "W4A4Linear", "quantize_opt", "quantize_llama_like", "quantize_model",
-    "save_packed_model", "load_packed_model",
+    "save_packed_model", "load_packed_model", "fold_mlp_permutation",
 ]
 
 SORT_KINDS = ("max", "mean3std", "argmax", "none")
@@ -182,7 +182,8 @@ def _shared_act(x_orig, xin, mod):
                     if e["left"] <= 0:
                         del _ACT_CACHE["entries"][slot]
                 return a
-    a = ops.quant_rows(xin, mod.perm, mod.sal_sorted, mod.group_size, mod.quant_bits,
+    perm, sal = mod.exec_partition()
+    a = ops.quant_rows(xin, perm, sal, mod.group_size, mod.quant_bits,
                        Kn=0 if mod.perm is None else mod.perm.numel(), int_groups=mod.int_groups)
     if pid is not None and (share is None or share > 1):
         with _ACT_LOCK:
@@ -242,8 +243,9 @@ class W4A4Linear(nn.Module):
         self.register_buffer("_weight", torch.empty((out_features, in_features), dtype=dtype, device=device))
         self.register_buffer("bias", torch.zeros((1, out_features), dtype=dtype, device=device) if bias else None)
         # fused-mode operands (filled by from_float)
-        for name in ("w_codes", "w_scales", "w_sal", "perm", "sal_sorted", "keep"):
+        for name in ("w_codes", "w_scales", "w_sal", "perm", "sal_sorted", "keep", "out_perm", "sal_exec"):
             self.register_buffer(name, None)
+        self.input_folded = False           # the producer already emits [perm columns | salient columns] (fold_mlp_permutation)
         self.int_groups = None              # fused mode: groups kept as integer codes (hybrid engine), set by the packer
         self.int_fraction = None
         self.salient_indices = None
@@ -284,6 +286,63 @@ class W4A4Linear(nn.Module):
             self.sal_sorted = sal.to(device=device, dtype=torch.int32)
             self.keep = torch.nonzero(mask).flatten().to(device=device, dtype=torch.int32)
         return self.sal_sorted, self.keep
+
+    def exec_partition(self):
+        """(perm, sal) the activation quantiser runs with.  Normally the layer's own lists (original column ids); when
+        the producer of x already emits the columns as [perm | salient] (fold_mlp_permutation) the permutation is the
+        identity over the first Kn columns (None: K1's contiguous mode, no gather) and the salient set is the tail."""
+        if not self.input_folded:
+            return self.perm, self.sal_sorted
+        return None, self.sal_exec
+
+    @torch.no_grad()
+    def fold_input_(self):
+        """Declare that x arrives as x_orig[:, concat(perm, sal_sorted)].  Returns that column order (int64) for the
+        producer to adopt.  The packed weight is untouched: it is stored in permuted order already."""
+        if self.mode != "fused" or self.w_codes is None:
+            raise ValueError("only packed mode='fused' layers can fold their input permutation")
+        if self.input_folded:
+            raise RuntimeError("input permutation already folded")
+        dev = self.w_codes.device
+        kn = self.perm.numel()
+        parts = [self.perm.long()]
+        if self.sal_sorted is not None:
+            parts.append(self.sal_sorted.long())
+        sigma = torch.cat(parts)
+        if sigma.numel() != self.in_features:
+            raise ValueError("permutation + salient set do not cover every input column")
+        ks = self.in_features - kn
+        self.sal_exec = torch.arange(kn, self.in_features, dtype=torch.int32, device=dev) if ks else None
+        self.input_folded = True
+        self._partition_id = ("folded",) + tuple(self._partition_id)
+        return sigma
+
+    @torch.no_grad()
+    def permute_outputs_(self, sigma):
+        """Emit y[:, sigma] instead of y: reorder the rows of the packed weight (codes, group scales, salient slice)
+        and the bias.  Each output element keeps its own dot product, so values are bit-identical, only their column
+        changes.  Composes with an earlier call."""
+        if self.mode != "fused" or self.w_codes is None:
+            raise ValueError("only packed mode='fused' layers can permute their outputs")
+        if self.tp_world != 1:
+            raise RuntimeError("permute the outputs before sharding")
+        if self.output_quant_name != "None":
+            raise ValueError("an output-quantised layer must keep its column order (fake_quant.py:309-316)")
+        N = self.out_features
+        sigma = torch.as_tensor(sigma).to(device=self.w_codes.device, dtype=torch.long)
+        _validate_columns(sigma, N, "output permutation")
+        if sigma.numel() != N:
+            raise ValueError(f"output permutation must list all {N} output channels")
+        self.w_codes = self.w_codes[sigma].contiguous()
+        if self.w_sal is not None:
+            self.w_sal = self.w_sal[sigma].contiguous()
+        sc = torch.zeros_like(self.w_scales)
+        sc[:, :N] = self.w_scales[:, :N][:, sigma]
+        self.w_scales = sc
+        if self.bias is not None:
+            self._buffers["bias"] = self.bias.reshape(-1)[sigma].contiguous().view(self.bias.shape)
+        self.out_perm = sigma if self.out_perm is None else self.out_perm[sigma]
+        return self
 
     # ---- activation / output fake quantiser of mode="reference" (fake_quant.py:291-304, :309-316)
     def _fake_quant_nonsalient(self, t2d, name, perm=None):
@@ -487,6 +546,10 @@ class W4A4Linear(nn.Module):
             out[:, self.perm.long()] = deq[:, :Kn]
         if ks:
             out[:, self.sal_sorted.long()] = self.w_sal[:, :ks]
+        if self.out_perm is not None:                 # rows are stored in emitted order: present the original order
+            orig = torch.empty_like(out)
+            orig[self.out_perm] = out
+            out = orig
         return out
 
     def packed_bytes(self) -> int:
@@ -517,8 +580,10 @@ class W4A4Linear(nn.Module):
         meta = dict(format=PACKED_FORMAT, in_features=self.in_features, out_features=self.out_features,
                     group_size=self.group_size, quant_bits=self.quant_bits, mode=self.mode, sort=self.sort,
                     act_quant=self.act_quant_name, weight_quant=self.weight_quant_name,
-                    output_quant=self.output_quant_name, int_groups=self.int_groups, int_fraction=self.int_fraction)
-        st = {"meta": meta, "bias": cpu(self.bias), "salient_indices": cpu(self.salient_indices)}
+                    output_quant=self.output_quant_name, int_groups=self.int_groups, int_fraction=self.int_fraction,
+                    input_folded=self.input_folded)
+        st = {"meta": meta, "bias": cpu(self.bias), "salient_indices": cpu(self.salient_indices),
+              "out_perm": cpu(self.out_perm)}
         if self.mode == "fused" and self.w_codes is not None:
             sdt = self.w_sal.dtype if self.w_sal is not None else torch.float32
             sc16 = self.w_scales.to(sdt)
@@ -565,7 +630,11 @@ class W4A4Linear(nn.Module):
                 new.w_codes = put(state["w_codes8"]).contiguous()
             new.w_scales = put(state["w_scales"]).float().contiguous()
             new.w_sal, new.perm = put(state["w_sal"]), put(state["perm"])
+            new.out_perm = put(state.get("out_perm"))
             new._set_partition_id()
+            if meta.get("input_folded"):
+                new._device_indices(dev)
+                new.fold_input_()
         else:
             new._buffers["_weight"] = put(state["weight"])
         new._device_indices(dev)
@@ -601,6 +670,20 @@ def _swap(parent, attr, prefix, input_feat, guarded, quantize_output, kw, extra)
         sort_key=None if sk is None else sk.get(prefix + "." + attr),
         mode=extra.get("mode", "reference"), sort=extra.get("sort", "max"), tp_group=extra.get("tp_group"),
         int_fraction=extra.get("int_fraction"), **kw))
+
+
+@torch.no_grad()
+def fold_mlp_permutation(gate_proj, up_proj, down_proj):
+    """fold down_proj's static input permutation into its producers.  down_proj consumes
+    act(gate(x)) * up(x), an elementwise function of the two outputs, so emitting gate / up channels in the order
+    [perm_down | salient_down] makes down_proj's activation arrive already partitioned: its quantiser reads contiguous
+    16-byte vectors instead of gathering 2-byte elements (K1 contiguous mode, 1.7x faster at K = 11008) and the model
+    output is bit-identical (every dot product is unchanged).  Reference anchor: smooth.py:126-141 (which producer
+    feeds which linears), fake_quant.py:291-301 (the gather this removes)."""
+    sigma = down_proj.fold_input_()
+    gate_proj.permute_outputs_(sigma)
+    up_proj.permute_outputs_(sigma)
+    return sigma
 
 
 def _mark_shared(parent, attrs):
@@ -645,6 +728,8 @@ def quantize_llama_like(model, weight_quant="per_channel", act_quant="per_token"
         if isinstance(m, (LlamaMLP, MistralMLP)):
             for attr in ("gate_proj", "up_proj", "down_proj"):
                 _swap(m, attr, prefix, input_feat, True, False, kw, extra)
+            if extra.get("fold") and extra.get("mode") == "fused" and extra.get("tp_group") is None:
+                fold_mlp_permutation(m.gate_proj, m.up_proj, m.down_proj)
             _mark_shared(m, ("gate_proj", "up_proj"))
             _mark_shared(m, ("down_proj",))
         elif isinstance(m, (LlamaAttention, MistralAttention)):

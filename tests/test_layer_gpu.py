@@ -345,3 +345,56 @@ def test_output_quantised_layer_shards_column_parallel(fq):
     y = torch.cat(parts, dim=1)[:, :N]
     assert torch.equal(shards[0]._quantize_output(y.contiguous()), want)
     fq.clear_act_cache()
+
+
+def test_folded_mlp_permutation_is_bit_identical(fq, golden_models):
+    """gate / up emit their channels in down_proj's [perm | salient] order, down_proj quantises its
+    input without a gather.  A folded Llama model must equal the unfolded one bit for bit (logits and every
+    down_proj output), down_proj must run K1 with the identity permutation, and the packed checkpoint must carry the
+    folding."""
+    c = golden_models["llama"]
+    models = []
+    for fold in (False, True):
+        m = _build("llama", c["config"])
+        m.load_state_dict(c["state_smoothed"])
+        m = m.half().to(DEV)
+        fq.quantize_model(m, weight_quant="per_group", act_quant="per_group", input_feat=c["input_feat"],
+                          salient_prop=c["salient_prop"], group_size=c["group_size"], mode="fused", fold=fold)
+        models.append(m)
+    plain, folded = models
+    downs = {n: mod for n, mod in folded.named_modules() if n.endswith("down_proj")}
+    assert downs and all(d.input_folded and d.exec_partition()[0] is None for d in downs.values())
+    for n, d in downs.items():
+        sal = d.exec_partition()[1]
+        assert torch.equal(sal.cpu(), torch.arange(d.perm.numel(), d.in_features, dtype=torch.int32))
+        up = folded.get_submodule(n.replace("down_proj", "up_proj"))
+        sigma = torch.cat([d.perm.long(), d.sal_sorted.long()])
+        assert torch.equal(up.out_perm, sigma)
+        assert torch.equal(up.weight, plain.get_submodule(n.replace("down_proj", "up_proj")).weight)   # original order view
+    rec_p, rm_p = {}, []
+    rec_f, rm_f = {}, []
+    for rec, rm, m in ((rec_p, rm_p, plain), (rec_f, rm_f, folded)):
+        for n, mod in m.named_modules():
+            if n.endswith("down_proj") or n.endswith("up_proj"):
+                rm.append(mod.register_forward_hook(lambda mod, x, y, n=n, rec=rec: rec.__setitem__(n, y.clone())))
+    ids = c["ids"].to(DEV)
+    with torch.no_grad():
+        lp, lf = plain(ids).logits, folded(ids).logits
+    for h in rm_p + rm_f:
+        h.remove()
+    assert torch.equal(lp, lf)
+    for n in rec_p:
+        if n.endswith("down_proj"):
+            assert torch.equal(rec_p[n], rec_f[n]), n
+        else:                                                       # up_proj: same values, emitted in sigma order
+            d = folded.get_submodule(n.replace("up_proj", "down_proj"))
+            sigma = torch.cat([d.perm.long(), d.sal_sorted.long()])
+            assert torch.equal(rec_p[n][..., sigma], rec_f[n]), n
+    # checkpoint round trip keeps the folding
+    ck = fq.save_packed_model(folded)
+    skel = _build("llama", c["config"]).half()
+    back = fq.load_packed_model(skel, ck, DEV)
+    with torch.no_grad():
+        assert torch.equal(back(ids).logits, lf)
+    assert all(mod.input_folded for n, mod in back.named_modules() if n.endswith("down_proj"))
+    fq.clear_act_cache()
