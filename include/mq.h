@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define MQ_ABI_VERSION 1
+#define MQ_ABI_VERSION 2
 
 enum { MQ_F16 = 0, MQ_BF16 = 1, MQ_F32 = 2 };
 
@@ -138,22 +138,41 @@ int mq_unpack_int4(const uint8_t* packed, int64_t R, int64_t cols, int64_t ld_pa
  *     bias [N] in `dtype` or NULL;  y [M, ldy] in `dtype`.
  *     G == 0 runs the pure 16-bit GEMM (mode="reference": dequantised operands in a_sal / w_sal);
  *     Ks == 0 runs the pure integer path.  group_size must be 32, 64 or a multiple of 128.
+ *     No workspace: the kernel needs none.  TMA descriptors are cached inside the library per (pointer, shape, ld),
+ *     and the call touches neither the device nor the stream besides the launch, so it is CUDA-graph capturable.
  * ---------------------------------------------------------------------------------------------------------- */
-size_t mq_mixed_gemm_workspace_bytes(int64_t M, int64_t N);
 int mq_mixed_gemm(const int8_t* a_codes, int64_t lda, const float* a_scales, int64_t ld_as,
                   const void* a_sal, int64_t ld_asal,
                   const int8_t* w_codes, int64_t ldw, const float* w_scales, int64_t ld_ws,
                   const void* w_sal, int64_t ld_wsal,
                   const void* bias, int64_t M, int64_t N, int64_t G, int group_size, int64_t Ks,
-                  int dtype, void* y, int64_t ldy,
-                  void* workspace, size_t workspace_bytes, void* stream);
+                  int dtype, void* y, int64_t ldy, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * K2d  decode regime (M <= 64 tokens) of the same F.linear (fake_quant.py:306) with INT4-RESIDENT weights: the
+ *      weight operand is read as two's-complement nibbles -- 4 bits per non-salient weight, the reference's own
+ *      accounting (smoothquant/model_size.py:5-15) -- from a layout made once by mq_pack_decode:
+ *        nibbles [ceil(N/16) row tiles][ceil(G*g/256) blocks][4 units of 64 columns][32 lanes][16 bytes]
+ *        salient [ceil(N/16) row tiles][ceil(Ks/64) blocks][4 steps of 16 columns][32 lanes][16 bytes]
+ *      (a lane's 16 bytes are its mma.sync A-fragment registers).  mq_decode_weight_bytes gives
+ *      the two buffer sizes.  Activation operands, scales, bias and y are exactly those of mq_mixed_gemm; all groups
+ *      must be integer groups (no hybrid tail), quant_bits <= 4, group_size a multiple of 64.
+ * ---------------------------------------------------------------------------------------------------------- */
+int mq_decode_weight_bytes(int64_t N, int64_t G, int group_size, int64_t Ks, size_t* nib_bytes, size_t* sal_bytes);
+int mq_pack_decode(const int8_t* w_codes, int64_t ldw, const void* w_sal, int64_t ld_wsal, int64_t N, int64_t G,
+                   int group_size, int64_t Ks, int dtype, uint8_t* out_nib, uint8_t* out_sal, void* stream);
+int mq_decode_gemm(const int8_t* a_codes, int64_t lda, const float* a_scales, int64_t ld_as,
+                   const void* a_sal, int64_t ld_asal,
+                   const uint8_t* w_nib, const float* w_scales, int64_t ld_ws, const uint8_t* w_sal_dec,
+                   const void* bias, int64_t M, int64_t N, int64_t G, int group_size, int64_t Ks,
+                   int dtype, void* y, int64_t ldy, void* stream);
 
 /* tuning knobs (process-global, for benchmarks/tests): name in {"gemm_bn", "gemm_stages", "quant_rows_per_stage",
  * "quant_warps", "quant_force_generic", ...}; value 0 restores the default.  MQ_ERR_ARG for unknown names. */
 int mq_set_option(const char* name, int value);
 
-/* debug: every in-kernel barrier wait is bounded (2 s); one that expires records {code, block, thread, parity,
- * spins>>10, 0, 0, 0} instead of hanging the GPU.  These copy the record of the quantiser / GEMM kernels to
+/* debug: every in-kernel barrier wait is bounded (5 s); one that expires records {code, block, thread, parity,
+ * spins>>10, 0, 0, 0} and traps (sticky CUDA error on the stream) instead of hanging the GPU or returning garbage.  These copy the record of the quantiser / GEMM kernels to
  * out8_host (8 x uint32, HOST pointer) and clear it.  code == 0 means no fault.  They synchronise the device. */
 int mq_quant_fault(unsigned int* out8_host);
 int mq_gemm_fault(unsigned int* out8_host);

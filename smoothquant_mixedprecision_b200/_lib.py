@@ -34,9 +34,12 @@ SIGNATURES = {
     "mq_fakequant_tensor": (_i32, [_vp, _i64, _i32, _i32, _vp, _vp, _sz, _vp]),
     "mq_pack_int4": (_i32, [_vp, _i64, _i64, _i64, _vp, _i64, _vp]),
     "mq_unpack_int4": (_i32, [_vp, _i64, _i64, _i64, _vp, _i64, _vp]),
-    "mq_mixed_gemm_workspace_bytes": (_sz, [_i64, _i64]),
     "mq_mixed_gemm": (_i32, [_vp, _i64, _vp, _i64, _vp, _i64, _vp, _i64, _vp, _i64, _vp, _i64,
-                             _vp, _i64, _i64, _i64, _i32, _i64, _i32, _vp, _i64, _vp, _sz, _vp]),
+                             _vp, _i64, _i64, _i64, _i32, _i64, _i32, _vp, _i64, _vp]),
+    "mq_decode_weight_bytes": (_i32, [_i64, _i64, _i32, _i64, C.POINTER(_sz), C.POINTER(_sz)]),
+    "mq_pack_decode": (_i32, [_vp, _i64, _vp, _i64, _i64, _i64, _i32, _i64, _i32, _vp, _vp, _vp]),
+    "mq_decode_gemm": (_i32, [_vp, _i64, _vp, _i64, _vp, _i64, _vp, _vp, _i64, _vp, _vp, _i64, _i64, _i64, _i32, _i64,
+                              _i32, _vp, _i64, _vp]),
     "mq_set_option": (_i32, [C.c_char_p, _i32]),
     "mq_quant_fault": (_i32, [C.POINTER(C.c_uint)]),
     "mq_gemm_fault": (_i32, [C.POINTER(C.c_uint)]),

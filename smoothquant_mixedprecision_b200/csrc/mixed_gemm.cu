@@ -24,11 +24,8 @@
 //               while this tile's output is being rounded and stored) overlap the rescale.
 #include <cuda.h>
 
-#include <atomic>
-#include <mutex>
-#include <unordered_map>
-
 #include "common.cuh"
+#include "tma_host.cuh"
 #include "ptx.cuh"
 
 namespace {
@@ -732,105 +729,7 @@ teardown:
 }
 
 // ------------------------------------------------------------------------------------------------ host side
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
-                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
-                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-EncodeTiledFn get_encode_fn() {
-  static EncodeTiledFn fn = nullptr;
-  if (fn) return fn;
-  void* p = nullptr;
-  cudaDriverEntryPointQueryResult q;
-  if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
-      q != cudaDriverEntryPointSuccess || !p)
-    return nullptr;
-  fn = reinterpret_cast<EncodeTiledFn>(p);
-  return fn;
-}
-
-// 2-D row-major tensor [rows, cols] of `esize`-byte elements with leading dimension ld (elements); box = 128 bytes
-// of the inner dimension x box_rows rows, 128-byte swizzle.
-//
-// Descriptors are cached per (pointer, dtype, shape, ld, box): a CUtensorMap is a pure function of those values (it
-// holds the global address, no allocation handle), so an entry stays valid when the allocator hands the same address
-// out again.  The weight operand's three maps are encoded once per layer, the activation's once per distinct buffer
-// address -- with torch's caching allocator that is a handful of addresses per model -- instead of six driver calls
-// per launch.  Host-side only: nothing here touches the device or the stream, so a launch through
-// mq_mixed_gemm can be captured into a CUDA graph.
-struct MapKey {
-  const void* ptr;
-  int64_t rows, cols, ld;
-  int dt, esize, box_rows, box_cols;
-  bool operator==(const MapKey& o) const {
-    return ptr == o.ptr && rows == o.rows && cols == o.cols && ld == o.ld && dt == o.dt && esize == o.esize &&
-           box_rows == o.box_rows && box_cols == o.box_cols;
-  }
-};
-struct MapKeyHash {
-  size_t operator()(const MapKey& k) const {
-    uint64_t h = reinterpret_cast<uintptr_t>(k.ptr) * 0x9E3779B97F4A7C15ull;
-    auto mix = [&h](uint64_t v) { h = (h ^ v) * 0xFF51AFD7ED558CCDull; h ^= h >> 29; };
-    mix((uint64_t)k.rows); mix((uint64_t)k.cols); mix((uint64_t)k.ld);
-    mix(((uint64_t)k.dt << 48) | ((uint64_t)k.esize << 40) | ((uint64_t)k.box_rows << 16) | (uint64_t)k.box_cols);
-    return (size_t)h;
-  }
-};
-constexpr size_t kMapCacheMax = 8192;   // ~1.2 MB of descriptors; cleared wholesale when full
-std::mutex g_map_mutex;
-std::unordered_map<MapKey, CUtensorMap, MapKeyHash> g_map_cache;
-std::atomic<long long> g_map_hits{0}, g_map_misses{0};
-
-int make_map(CUtensorMap* map, const void* ptr, CUtensorMapDataType dt, int esize, int64_t rows, int64_t cols,
-             int64_t ld, int box_rows, int box_cols = 0) {
-  const MapKey key{ptr, rows, cols, ld, (int)dt, esize, box_rows, box_cols};
-  {
-    std::lock_guard<std::mutex> lk(g_map_mutex);
-    auto it = g_map_cache.find(key);
-    if (it != g_map_cache.end()) {
-      *map = it->second;
-      g_map_hits.fetch_add(1, std::memory_order_relaxed);
-      return MQ_OK;
-    }
-  }
-  EncodeTiledFn enc = get_encode_fn();
-  if (!enc) {
-    mq_set_error("cuTensorMapEncodeTiled entry point not available");
-    return MQ_ERR_CUDA;
-  }
-  cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
-  cuuint64_t strides[1] = {(cuuint64_t)ld * (cuuint64_t)esize};
-  // box_cols == 0: operand tile (128-byte rows, 128-byte swizzle); otherwise a plain row vector of box_cols elements
-  cuuint32_t box[2] = {(cuuint32_t)(box_cols ? box_cols : 128 / esize), (cuuint32_t)box_rows};
-  cuuint32_t estr[2] = {1, 1};
-  CUresult r = enc(map, dt, 2, const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                   box_cols ? CU_TENSOR_MAP_SWIZZLE_NONE : CU_TENSOR_MAP_SWIZZLE_128B,
-                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  if (r != CUDA_SUCCESS) {
-    mq_set_error("cuTensorMapEncodeTiled failed with CUresult %d (rows=%lld cols=%lld ld=%lld esize=%d)", (int)r,
-                 (long long)rows, (long long)cols, (long long)ld, esize);
-    return MQ_ERR_CUDA;
-  }
-  g_map_misses.fetch_add(1, std::memory_order_relaxed);
-  std::lock_guard<std::mutex> lk(g_map_mutex);
-  if (g_map_cache.size() >= kMapCacheMax) g_map_cache.clear();
-  g_map_cache.emplace(key, *map);
-  return MQ_OK;
-}
-
-// cudaFuncSetAttribute once per kernel instantiation and device (not per launch)
-int ensure_smem_attr(const void* kern, int bytes) {
-  static std::mutex mu;
-  static std::unordered_map<uint64_t, int> done;   // (function, device) -> bytes
-  int dev = 0;
-  MQ_CHECK_CUDA(cudaGetDevice(&dev));
-  const uint64_t key = (uint64_t)reinterpret_cast<uintptr_t>(kern) * 64u + (uint64_t)(dev & 63);
-  std::lock_guard<std::mutex> lk(mu);
-  auto it = done.find(key);
-  if (it != done.end() && it->second >= bytes) return MQ_OK;
-  MQ_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
-  done[key] = bytes;
-  return MQ_OK;
-}
+// tensor-map cache (mq_make_map) and the per-kernel shared-memory attribute helper live in tma_host.cu
 
 template <typename OutT, int BN, int kStages, bool kPair, bool kMagicMma>
 int launch_gemm_m(const CUtensorMap& ma, const CUtensorMap& mw, const CUtensorMap& mas, const CUtensorMap& mws,
@@ -840,7 +739,7 @@ int launch_gemm_m(const CUtensorMap& ma, const CUtensorMap& mw, const CUtensorMa
   p.profile = mq_get_option("gemm_profile", 0);
   auto kern = p.profile ? mixed_gemm_kernel<OutT, BN, kStages, true, kPair, kMagicMma>
                         : mixed_gemm_kernel<OutT, BN, kStages, false, kPair, kMagicMma>;
-  if (int rc = ensure_smem_attr(reinterpret_cast<const void*>(kern), L::kTotal)) return rc;
+  if (int rc = mq_ensure_smem_attr(reinterpret_cast<const void*>(kern), L::kTotal)) return rc;
   constexpr int TM = kPair ? 2 * BM : BM;
   p.tiles_m = (p.M + TM - 1) / TM;
   p.tiles_n = (p.N + BN - 1) / BN;
@@ -891,19 +790,10 @@ int dispatch_gemm(const CUtensorMap& ma, const CUtensorMap& mw, const CUtensorMa
 
 extern "C" {
 
-size_t mq_mixed_gemm_workspace_bytes(int64_t M, int64_t N) {
-  (void)M;
-  (void)N;
-  return 0;
-}
-
 int mq_mixed_gemm(const int8_t* a_codes, int64_t lda, const float* a_scales, int64_t ld_as, const void* a_sal,
                   int64_t ld_asal, const int8_t* w_codes, int64_t ldw, const float* w_scales, int64_t ld_ws,
                   const void* w_sal, int64_t ld_wsal, const void* bias, int64_t M, int64_t N, int64_t G,
-                  int group_size, int64_t Ks, int dtype, void* y, int64_t ldy, void* workspace,
-                  size_t workspace_bytes, void* stream) {
-  (void)workspace;
-  (void)workspace_bytes;
+                  int group_size, int64_t Ks, int dtype, void* y, int64_t ldy, void* stream) {
   MQ_CHECK_ARG(y && M >= 0 && N >= 1 && ldy >= N, "mq_mixed_gemm: bad output (M=%lld N=%lld ldy=%lld)", (long long)M,
                (long long)N, (long long)ldy);
   MQ_CHECK_ARG(dtype == MQ_F16 || dtype == MQ_BF16, "mq_mixed_gemm: dtype must be MQ_F16 or MQ_BF16");
@@ -944,16 +834,16 @@ int mq_mixed_gemm(const int8_t* a_codes, int64_t lda, const float* a_scales, int
   CUtensorMap ma, mw, mas, mws, msa, msw;
   int rc;
   if (G > 0) {
-    if ((rc = make_map(&ma, a_codes, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, M, kc, lda, BM))) return rc;
-    if ((rc = make_map(&mw, w_codes, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, N, kc, ldw, wbox))) return rc;
+    if ((rc = mq_make_map(&ma, a_codes, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, M, kc, lda, BM))) return rc;
+    if ((rc = mq_make_map(&mw, w_codes, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, N, kc, ldw, wbox))) return rc;
     // scale vectors: [G, M] / [G, N] fp32, one row of BM / BN values per unit (rows and columns past M / N read 0)
-    if ((rc = make_map(&msa, a_scales, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, G, M, ld_as, 1, BM))) return rc;
-    if ((rc = make_map(&msw, w_scales, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, G, N, ld_ws, 1, bn))) return rc;
+    if ((rc = mq_make_map(&msa, a_scales, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, G, M, ld_as, 1, BM))) return rc;
+    if ((rc = mq_make_map(&msw, w_scales, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, G, N, ld_ws, 1, bn))) return rc;
   }
   const CUtensorMapDataType dt16 = dtype == MQ_F16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
   if (Ks > 0) {  // the tensor maps cover exactly Ks columns: TMA zero-fills the tail of the last 64-column block
-    if ((rc = make_map(&mas, a_sal, dt16, 2, M, Ks, ld_asal, BM))) return rc;
-    if ((rc = make_map(&mws, w_sal, dt16, 2, N, Ks, ld_wsal, wbox))) return rc;
+    if ((rc = mq_make_map(&mas, a_sal, dt16, 2, M, Ks, ld_asal, BM))) return rc;
+    if ((rc = mq_make_map(&mws, w_sal, dt16, 2, N, Ks, ld_wsal, wbox))) return rc;
   } else {
     mas = ma;
     mws = mw;

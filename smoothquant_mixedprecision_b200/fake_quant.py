@@ -246,6 +246,7 @@ class W4A4Linear(nn.Module):
         for name in ("w_codes", "w_scales", "w_sal", "perm", "sal_sorted", "keep", "out_perm", "sal_exec"):
             self.register_buffer(name, None)
         self.input_folded = False           # the producer already emits [perm columns | salient columns] (fold_mlp_permutation)
+        self.w_decode = None                # ops.DecodeWeights: INT4-resident operand of the decode kernel (prepare_decode)
         self.int_groups = None              # fused mode: groups kept as integer codes (hybrid engine), set by the packer
         self.int_fraction = None
         self.salient_indices = None
@@ -261,7 +262,7 @@ class W4A4Linear(nn.Module):
     # the packed operands in fused mode
     @property
     def weight(self):
-        if self.mode == "fused" and self.w_codes is not None:
+        if self.mode == "fused" and (self.w_codes is not None or self.w_decode is not None):
             return self.dequantized_weight()
         return self._weight
 
@@ -398,6 +399,8 @@ class W4A4Linear(nn.Module):
         without it the layer returns its [M, N_local] column block (consumer is column-local)."""
         if self.tp_world != 1:
             raise RuntimeError("layer is already sharded")
+        if self.w_decode is not None:
+            raise RuntimeError("shard the layer before prepare_decode (the decode layout is built per shard)")
         if self.output_quant_name != "None" and not gather_output:
             raise ValueError("an output-quantised layer must gather its output: the output quantiser groups columns "
                              "across the whole width (fake_quant.py:309-316)")
@@ -420,15 +423,79 @@ class W4A4Linear(nn.Module):
         return self
 
     def _forward_fused(self, x, x2):
-        cdt = self.w_sal.dtype if self.w_sal is not None else (
-            x2.dtype if x2.dtype in (torch.float16, torch.bfloat16) else torch.float16)
+        cdt = self.w_sal.dtype if self.w_sal is not None else (self.w_decode.dtype if self.w_decode is not None else (
+            x2.dtype if x2.dtype in (torch.float16, torch.bfloat16) else torch.float16))
         xin = x2 if x2.dtype == cdt else x2.to(cdt)
         # layers fed by the same tensor with the same K partition (q/k/v, gate/up: same calibration statistics in
         # the reference, fake_quant.py:396-455) share one quantised activation
         a = _shared_act(x, xin, self)
+        if self.w_decode is not None and a.rows <= ops.DECODE_MAX_TOKENS:
+            return ops.decode_gemm(a, self.w_decode, self.bias)      # weight-bandwidth regime: int4-resident weights
+        if self.w_codes is None:
+            self._restore_prefill_operand()          # stays resident from now on: the layer serves both regimes
         w = ops.QuantizedRows(codes=self.w_codes, scales=self.w_scales, sal=self.w_sal, rows=self.out_features,
                               Kn=a.Kn, Ks=a.Ks, group_size=self.group_size, int_groups=a.int_groups)
         return ops.mixed_gemm(a, w, self.bias, out_dtype=cdt)
+
+    # ---- decode regime: INT4-resident weights (BASELINE config 5; no reference counterpart beyond F.linear :306)
+    @torch.no_grad()
+    def prepare_decode(self, keep_prefill=True):
+        """Build the nibble layout the decode kernel (M <= 64 tokens) streams: 4 bits per non-salient weight on the
+        device (smoothquant/model_size.py:5-15's accounting made real).  With ``keep_prefill=False`` the int8 codes of
+        the prefill kernel are released -- the layer then holds ~0.5 byte per weight; a later forward with more than 64
+        tokens rebuilds them from the nibbles (mq_unpack_int4 of a plain nibble copy kept at 0.5 byte per weight would
+        double the footprint, so the rebuild re-reads the decode layout instead)."""
+        if self.mode != "fused" or self.w_codes is None:
+            raise ValueError("prepare_decode needs a packed mode='fused' layer")
+        G = (self.perm.numel() + self.group_size - 1) // self.group_size
+        if not ops.decode_supported(self.group_size, self.int_groups, G, self.quant_bits):
+            raise ValueError("the decode kernel needs integer groups only, quant_bits <= 4 and a group size that is a "
+                             f"multiple of 64 (group_size={self.group_size}, int_groups={self.int_groups}/{G}, "
+                             f"quant_bits={self.quant_bits})")
+        ks = 0 if self.sal_sorted is None else self.sal_sorted.numel()
+        wq = ops.QuantizedRows(codes=self.w_codes, scales=self.w_scales, sal=self.w_sal, rows=self.out_features,
+                               Kn=self.perm.numel(), Ks=ks, group_size=self.group_size, int_groups=G, n_salient=ks)
+        self.w_decode = ops.pack_decode(wq)
+        if not keep_prefill:
+            self.w_codes = None
+            self.w_sal = None
+        return self
+
+    def _restore_prefill_operand(self):
+        """Rebuild the prefill kernel's int8 codes / row-major salient slice from the decode layout (a fixed index
+        permutation, inverted with tensor views; offline path -- only taken when a layer prepared with
+        keep_prefill=False is asked for more than 64 tokens, its dequantised weight or a checkpoint)."""
+        d = self.w_decode
+        if d is None:
+            raise RuntimeError("layer holds neither prefill codes nor a decode layout")
+        N, G, g = self.out_features, d.groups, d.group_size
+        tiles = (N + 15) // 16
+        nib = d.nib.view(tiles, -1, 8, 4, 2, 2, 4)                          # [tile, unit, gid, tq, pk, pr, j]
+        units = nib.shape[1]
+        both = torch.stack(((nib & 15), (nib >> 4)), dim=-1).to(torch.int8)  # [..., j, hl]: low nibble k, high k + 32
+        both = ((both ^ 8) - 8)                                              # two's-complement nibble -> int8
+        codes = both.permute(0, 5, 2, 1, 7, 4, 3, 6).reshape(tiles * 16, units * 64)[:N]
+        ld = max((G * g + 127) // 128 * 128, 128)
+        out = torch.zeros((N, ld), dtype=torch.int8, device=d.nib.device)
+        out[:, : G * g] = codes[:, : G * g]
+        self.w_codes = out
+        if d.Ks:
+            sal = d.sal.view(d.dtype).view(tiles, -1, 8, 4, 2, 2, 2)        # [tile, step, gid, tq, pk, pr, h]
+            steps = sal.shape[1]
+            rows = sal.permute(0, 5, 2, 1, 4, 3, 6).reshape(tiles * 16, steps * 16)[:N]
+            ws = torch.zeros((N, (d.Ks + 7) // 8 * 8), dtype=d.dtype, device=d.nib.device)
+            ws[:, : d.Ks] = rows[:, : d.Ks]
+            self.w_sal = ws
+
+    def device_weight_bytes(self) -> int:
+        """Bytes this layer's weight operands occupy on the device right now (all resident copies)."""
+        n = 0
+        for t in (self.w_codes, self.w_scales, self.w_sal, self._weight):
+            if t is not None:
+                n += t.numel() * t.element_size()
+        if self.w_decode is not None:
+            n += self.w_decode.nib.numel() + (0 if self.w_decode.sal is None else self.w_decode.sal.numel())
+        return n
 
     def _forward_reference(self, x2, act_perm):
         q_x = self._fake_quant_nonsalient(x2, self.act_quant_name, act_perm)
@@ -528,6 +595,17 @@ class W4A4Linear(nn.Module):
     def dequantized_weight(self):
         """[N, K] weight equivalent to the packed operands: code*scale at the original column of every permuted
         position, the FP salient columns elsewhere (API compatibility; not on the hot path)."""
+        released = self.w_codes is None
+        if released:
+            self._restore_prefill_operand()
+        try:
+            return self._dequantized_weight()
+        finally:
+            if released:
+                self.w_codes = None
+                self.w_sal = None
+
+    def _dequantized_weight(self):
         N, K, g = self.out_features, self.in_features, self.group_size
         Kn = self.perm.numel()
         G = (Kn + g - 1) // g
@@ -584,6 +662,8 @@ class W4A4Linear(nn.Module):
                     input_folded=self.input_folded)
         st = {"meta": meta, "bias": cpu(self.bias), "salient_indices": cpu(self.salient_indices),
               "out_perm": cpu(self.out_perm)}
+        if self.mode == "fused" and self.w_codes is None and self.w_decode is not None:
+            self._restore_prefill_operand()          # the checkpoint format is the row-major nibble format
         if self.mode == "fused" and self.w_codes is not None:
             sdt = self.w_sal.dtype if self.w_sal is not None else torch.float32
             sc16 = self.w_scales.to(sdt)

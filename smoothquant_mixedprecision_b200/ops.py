@@ -285,7 +285,7 @@ def mixed_gemm(a: Optional[QuantizedRows], w: Optional[QuantizedRows], bias: Opt
             _ptr(w.codes) if G else None, w.codes.stride(0) if G else 0,
             _ptr(w.scales) if G else None, w.scales.stride(0) if G else 0,
             _ptr(w_sal) if Ks else None, w_sal.stride(0) if Ks else 0,
-            _ptr(bias), M, N, G, g, Ks, _DTYPES[dt], y.data_ptr(), y.stride(0), None, 0,
+            _ptr(bias), M, N, G, g, Ks, _DTYPES[dt], y.data_ptr(), y.stride(0),
             torch.cuda.current_stream(dev).cuda_stream), "mq_mixed_gemm")
     if ev is not None:
         ev[1].record(torch.cuda.current_stream(dev))
@@ -296,4 +296,79 @@ def mixed_gemm(a: Optional[QuantizedRows], w: Optional[QuantizedRows], bias: Opt
         if a is not None and G * g < a.Kn:
             ks_true += a.Kn - G * g
         GEMM_EVENTS.append((ev[0], ev[1], 2.0 * M * N * kn_int, 2.0 * M * N * ks_true))
+    return y[:, :N]
+
+
+# ---------------------------------------------------------------------------------------------- K2d (decode, int4)
+DECODE_MAX_TOKENS = 64
+DECODE_EVENTS = None        # set to a list to collect (start_event, end_event, weight_bytes) per mq_decode_gemm
+
+
+@dataclass
+class DecodeWeights:
+    """INT4-resident weight operand of the decode kernel (mq_pack_decode layout)."""
+    nib: torch.Tensor              # uint8 [tiles * blocks * 2048]   two codes per byte
+    sal: Optional[torch.Tensor]    # uint8 [tiles * sal_blocks * 2048] salient slice (16-bit values), mma fragment order
+    scales: torch.Tensor           # fp32  [G, ld_ws] group-major (shared with the prefill operand)
+    rows: int
+    groups: int
+    group_size: int
+    Ks: int                        # salient columns
+    dtype: torch.dtype
+
+    def nbytes(self) -> int:
+        return self.nib.numel() + (0 if self.sal is None else self.sal.numel()) + self.scales.numel() * 4
+
+
+def decode_supported(group_size: int, int_groups: Optional[int], groups: int, n_bits: int) -> bool:
+    return group_size >= 64 and group_size % 64 == 0 and groups >= 1 and (int_groups is None or int_groups == groups) \
+        and n_bits <= 4
+
+
+def pack_decode(w: QuantizedRows) -> DecodeWeights:
+    """int8 codes [N, ld] + salient [N, ld_sal] of the prefill operand -> the nibble layout the decode kernel streams."""
+    _need_cuda(w.codes, w.sal)
+    N, G, g = w.rows, w.groups, w.group_size
+    Ks = 0 if w.sal is None else (w.n_salient if w.n_salient is not None else w.Ks)
+    dt = w.sal.dtype if w.sal is not None else torch.float16
+    import ctypes as C
+    nb, sb = C.c_size_t(0), C.c_size_t(0)
+    _check(lib.mq_decode_weight_bytes(N, G, g, Ks, C.byref(nb), C.byref(sb)), "mq_decode_weight_bytes")
+    dev = w.codes.device
+    nib = torch.empty(nb.value, dtype=torch.uint8, device=dev)
+    sal = torch.empty(sb.value, dtype=torch.uint8, device=dev) if Ks else None
+    with torch.cuda.device(dev):
+        check(lib.mq_pack_decode(w.codes.data_ptr(), w.codes.stride(0), _ptr(w.sal) if Ks else None,
+                                 w.sal.stride(0) if Ks else 0, N, G, g, Ks, _DTYPES[dt], nib.data_ptr(), _ptr(sal),
+                                 torch.cuda.current_stream(dev).cuda_stream), "mq_pack_decode")
+    return DecodeWeights(nib=nib, sal=sal, scales=w.scales, rows=N, groups=G, group_size=g, Ks=Ks, dtype=dt)
+
+
+def decode_gemm(a: QuantizedRows, w: DecodeWeights, bias: Optional[torch.Tensor]) -> torch.Tensor:
+    """y for M <= 64 tokens from int4-resident weights (same contract as mixed_gemm; fake_quant.py:306)."""
+    M, N, G, g = a.rows, w.rows, w.groups, w.group_size
+    if M > DECODE_MAX_TOKENS:
+        raise ValueError(f"decode_gemm handles at most {DECODE_MAX_TOKENS} tokens, got {M}")
+    if a.groups != G or a.group_size != g or (a.n_salient if a.n_salient is not None else a.Ks) != w.Ks:
+        raise ValueError("activation / weight group partitions differ")
+    dev = a.codes.device
+    dt = w.dtype
+    if w.Ks and a.sal.dtype != dt:
+        raise TypeError("salient slices of activation and weight must share a dtype")
+    if bias is not None:
+        bias = bias.reshape(-1).to(device=dev, dtype=dt).contiguous()
+    y = torch.empty((M, _round_up(N, 8)), dtype=dt, device=dev)
+    ev = None
+    if DECODE_EVENTS is not None:
+        ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+        ev[0].record(torch.cuda.current_stream(dev))
+    with torch.cuda.device(dev):
+        check(lib.mq_decode_gemm(a.codes.data_ptr(), a.codes.stride(0), a.scales.data_ptr(), a.scales.stride(0),
+                                 _ptr(a.sal) if w.Ks else None, a.sal.stride(0) if w.Ks else 0,
+                                 w.nib.data_ptr(), w.scales.data_ptr(), w.scales.stride(0), _ptr(w.sal), _ptr(bias),
+                                 M, N, G, g, w.Ks, _DTYPES[dt], y.data_ptr(), y.stride(0),
+                                 torch.cuda.current_stream(dev).cuda_stream), "mq_decode_gemm")
+    if ev is not None:
+        ev[1].record(torch.cuda.current_stream(dev))
+        DECODE_EVENTS.append((ev[0], ev[1], w.nbytes()))
     return y[:, :N]

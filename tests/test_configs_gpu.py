@@ -105,6 +105,11 @@ def _check_fused_layer_sampled(fq, ops, mod, x, w_cpu, bias_cpu, imp, key, g, p,
     assert err <= tol, (tag, err, tol)
 
 
+def _sampled_oracle_y(x, w_cpu, bias_cpu, imp, key, g, p, rows):
+    part = O.fused_partition(x.shape[-1], O.select_salient(imp, p) if p > 0 else None, key, g)
+    return O.fused_layer_oracle(x[rows.to(DEV)].cpu(), w_cpu, bias_cpu, part)[0]
+
+
 # ------------------------------------------------------------------------------------------------ configs 4 / 5
 SHAPES45 = [(11008, 4096), (4096, 11008), (13824, 5120), (1024, 8192), (28672, 8192), (8192, 28672)]   # (N, K)
 MS45 = [1, 8, 16, 64, 256, 4096, 32768]
@@ -134,6 +139,18 @@ def test_config45_gemm_sweep_sampled(fq, ops, M, N, K, g, p):
     # the oracle sees only the sampled output channels: index them 0..n-1
     _check_fused_layer_sampled(fq, ops, _ColView(mod, cols), x, w_cpu, bias_cpu, imp, key, g, p, rows,
                                torch.arange(cols.numel()), f"cfg45 M={M} N={N} K={K} g={g} p={p}")
+    if M <= 64:
+        # decode regime (config 5): the same layer from INT4-resident weights (mq_decode_gemm), prefill codes released
+        before = mod.device_weight_bytes()
+        mod.prepare_decode(keep_prefill=False)
+        assert mod.w_codes is None and mod.w_decode is not None and mod.device_weight_bytes() < 0.62 * before
+        view = _ColView.__new__(_ColView)
+        view.mod, view.c, view.out_features = mod, cols.to(DEV), cols.numel()
+        y64 = _sampled_oracle_y(x, w_cpu, bias_cpu, imp, key, g, p, rows)
+        got = mod(x)[rows.to(DEV)][:, cols.to(DEV)].double().cpu()
+        err, tol = float((got - y64).abs().max()), 1e-3 * float(y64.abs().max()) + 1e-3
+        _log(test=f"cfg45 decode M={M} N={N} K={K} g={g} p={p}", err=err, tol=tol)
+        assert err <= tol, (err, tol)
     del mod, lin, x
     fq.clear_act_cache()
 

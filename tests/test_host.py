@@ -20,7 +20,8 @@ def test_library_exports_every_declared_symbol():
     assert declared == set(_lib.SIGNATURES), declared ^ set(_lib.SIGNATURES)
     for name in declared:
         assert hasattr(_lib.lib, name), name
-    assert _lib.lib.mq_version() == 1
+    m = re.search(r"#define MQ_ABI_VERSION (\d+)", open(os.path.join(ROOT, "include", "mq.h")).read())
+    assert _lib.lib.mq_version() == int(m.group(1)) == 2
     assert _lib.lib.mq_set_option(b"no_such_option", 1) == -1
     assert b"unknown option" in _lib.lib.mq_last_error()
 

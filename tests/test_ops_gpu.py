@@ -436,3 +436,70 @@ def test_cta_pair_kernel_is_bit_identical_to_single_cta_kernel(ops, mqlib, M, N,
     torch.cuda.synchronize()
     assert mqlib.gemm_fault()[0] == 0
     assert torch.equal(y0, y1)
+
+
+# ------------------------------------------------------------------------------------------------ K2d (decode, int4)
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("M,N,K,g,p", [(1, 256, 512, 128, 0.05), (5, 1000, 1024, 64, 0.1), (8, 4096, 4096, 128, 0.05),
+                                       (16, 520, 2048, 256, 0.0), (24, 11008, 4096, 128, 0.05), (33, 4096, 11008, 128, 0.05),
+                                       (64, 1024, 8192, 1024, 0.1), (64, 8192, 8192, 128, 0.1), (3, 72, 320, 64, 0.3)])
+def test_decode_gemm_matches_prefill_kernel_and_composed_reference(ops, mqlib, M, N, K, g, p, dtype):
+    """mq_decode_gemm (INT4-resident weights, mma.sync swap-AB) against the prefill kernel on the same operands and
+    against the fp64 composition of the codes / scales.  The integer part is the same arithmetic operation for
+    operation; the salient slice differs only in fp32 summation order -> 2 ulp of the output type."""
+    x = synth(M, K, dtype, seed=M + N)
+    gen = torch.Generator().manual_seed(N + K)
+    w = (torch.randn(N, K, generator=gen) * 0.05).to(dtype)
+    bias = (torch.randn(N, generator=gen) * 0.1).to(dtype)
+    order = torch.randperm(K, generator=gen)
+    ks = max(1, int(p * K)) if p > 0 else 0
+    perm = order[ks:].to(DEV)
+    sal = torch.sort(order[:ks]).values.to(DEV) if ks else None
+    a = ops.quant_rows(x.to(DEV), perm, sal, g)
+    wq = ops.quant_rows(w.to(DEV), perm, sal, g)
+    dw = ops.pack_decode(wq)
+    Kn, G = K - ks, (K - ks + g - 1) // g
+    assert dw.nib.numel() == ((N + 15) // 16) * ((G * g + 255) // 256) * 2048       # 0.5 byte per (padded) weight
+    y_dec = ops.decode_gemm(a, dw, bias.to(DEV))
+    y_pre = ops.mixed_gemm(a, wq, bias.to(DEV))
+    torch.cuda.synchronize()
+    assert y_dec.shape == (M, N) and y_dec.dtype == dtype
+    ref = _gemm_reference(a, wq, bias.to(DEV), ks, M, N).double()
+    scale = float(ref.abs().max())
+    tol = (8e-3 if dtype == torch.bfloat16 else 1e-3) * scale + 1e-3
+    assert float((y_dec.double() - ref).abs().max()) <= tol
+    ulp = 2.0 ** (-7 if dtype == torch.bfloat16 else -10)
+    assert float((y_dec.float() - y_pre.float()).abs().max()) <= 2 * ulp * scale
+    if ks == 0:
+        assert torch.equal(y_dec, y_pre)          # integer part: bit-identical to the prefill kernel
+
+
+def test_decode_layer_releases_prefill_codes_and_rebuilds_them(ops):
+    """W4A4Linear.prepare_decode(keep_prefill=False): the layer keeps 4 bits per non-salient weight on the device, runs
+    M <= 64 through the decode kernel, and rebuilds the prefill operand bit for bit when a longer batch arrives."""
+    from smoothquant_mixedprecision_b200 import fake_quant as fq
+    torch.manual_seed(3)
+    K, N, g = 2048, 1536, 128
+    lin = torch.nn.Linear(K, N).half().to(DEV)
+    imp = torch.rand(K)
+    mod = fq.W4A4Linear.from_float(lin, "per_group", "per_group", importance=imp, salient_prop=0.05, group_size=g,
+                                   mode="fused", sort_key=imp)
+    x16 = torch.randn(16, K, device=DEV).half()
+    x300 = torch.randn(300, K, device=DEV).half()
+    y16, y300, wd = mod(x16).clone(), mod(x300).clone(), mod.weight.clone()
+    codes, wsal, full = mod.w_codes.clone(), mod.w_sal.clone(), mod.device_weight_bytes()
+    mod.prepare_decode(keep_prefill=False)
+    assert mod.w_codes is None and mod.w_sal is None
+    assert mod.device_weight_bytes() < 0.62 * full
+    assert torch.equal(mod.weight, wd)                         # dequantised view from the nibble layout
+    assert mod.w_codes is None                                 # ... without keeping the rebuilt operand
+    yd = mod(x16)
+    assert float((yd.float() - y16.float()).abs().max()) <= 2 * 2.0 ** -10 * float(y16.abs().max())
+    assert torch.equal(mod(x300), y300)                        # > 64 tokens: prefill operand rebuilt, bit-identical
+    assert torch.equal(mod.w_codes, codes) and torch.equal(mod.w_sal, wsal)
+    st = mod.packed_state()
+    back = fq.W4A4Linear.from_packed(st, DEV)
+    assert torch.equal(back(x300), y300)
+    with pytest.raises(ValueError):
+        fq.W4A4Linear.from_float(lin, "per_group", "per_group", group_size=32, mode="fused").prepare_decode()
+    fq.clear_act_cache()
