@@ -152,18 +152,21 @@ int mq_mixed_gemm(const int8_t* a_codes, int64_t lda, const float* a_scales, int
  * K2d  decode regime (M <= 64 tokens) of the same F.linear (fake_quant.py:306) with INT4-RESIDENT weights: the
  *      weight operand is read as two's-complement nibbles -- 4 bits per non-salient weight, the reference's own
  *      accounting (smoothquant/model_size.py:5-15) -- from a layout made once by mq_pack_decode:
- *        nibbles [ceil(N/16) row tiles][ceil(G*g/256) blocks][4 units of 64 columns][32 lanes][16 bytes]
+ *        nibbles [ceil(N/16) row tiles][ceil(G*g/256) blocks] records of 2048 + 32 * max(1, 256/g) bytes: the
+ *                block's nibbles as [4 units of 64 columns][32 lanes][16 bytes], then the weight scales of the
+ *                groups in the block as [slot][16 rows] values of `dtype` (exact: the scales are values of it)
  *        salient [ceil(N/16) row tiles][ceil(Ks/64) blocks][4 steps of 16 columns][32 lanes][16 bytes]
  *      (a lane's 16 bytes are its mma.sync A-fragment registers).  mq_decode_weight_bytes gives
- *      the two buffer sizes.  Activation operands, scales, bias and y are exactly those of mq_mixed_gemm; all groups
- *      must be integer groups (no hybrid tail), quant_bits <= 4, group_size a multiple of 64.
+ *      the two buffer sizes.  Activation operands, bias and y are exactly those of mq_mixed_gemm; all groups must be
+ *      integer groups (no hybrid tail), quant_bits <= 4, group_size a power of two >= 64.
  * ---------------------------------------------------------------------------------------------------------- */
 int mq_decode_weight_bytes(int64_t N, int64_t G, int group_size, int64_t Ks, size_t* nib_bytes, size_t* sal_bytes);
-int mq_pack_decode(const int8_t* w_codes, int64_t ldw, const void* w_sal, int64_t ld_wsal, int64_t N, int64_t G,
+int mq_pack_decode(const int8_t* w_codes, int64_t ldw, const float* w_scales, int64_t ld_ws,
+                   const void* w_sal, int64_t ld_wsal, int64_t N, int64_t G,
                    int group_size, int64_t Ks, int dtype, uint8_t* out_nib, uint8_t* out_sal, void* stream);
 int mq_decode_gemm(const int8_t* a_codes, int64_t lda, const float* a_scales, int64_t ld_as,
                    const void* a_sal, int64_t ld_asal,
-                   const uint8_t* w_nib, const float* w_scales, int64_t ld_ws, const uint8_t* w_sal_dec,
+                   const uint8_t* w_nib, const uint8_t* w_sal_dec,
                    const void* bias, int64_t M, int64_t N, int64_t G, int group_size, int64_t Ks,
                    int dtype, void* y, int64_t ldy, void* stream);
 

@@ -37,8 +37,8 @@ SIGNATURES = {
     "mq_mixed_gemm": (_i32, [_vp, _i64, _vp, _i64, _vp, _i64, _vp, _i64, _vp, _i64, _vp, _i64,
                              _vp, _i64, _i64, _i64, _i32, _i64, _i32, _vp, _i64, _vp]),
     "mq_decode_weight_bytes": (_i32, [_i64, _i64, _i32, _i64, C.POINTER(_sz), C.POINTER(_sz)]),
-    "mq_pack_decode": (_i32, [_vp, _i64, _vp, _i64, _i64, _i64, _i32, _i64, _i32, _vp, _vp, _vp]),
-    "mq_decode_gemm": (_i32, [_vp, _i64, _vp, _i64, _vp, _i64, _vp, _vp, _i64, _vp, _vp, _i64, _i64, _i64, _i32, _i64,
+    "mq_pack_decode": (_i32, [_vp, _i64, _vp, _i64, _vp, _i64, _i64, _i64, _i32, _i64, _i32, _vp, _vp, _vp]),
+    "mq_decode_gemm": (_i32, [_vp, _i64, _vp, _i64, _vp, _i64, _vp, _vp, _vp, _i64, _i64, _i64, _i32, _i64,
                               _i32, _vp, _i64, _vp]),
     "mq_set_option": (_i32, [C.c_char_p, _i32]),
     "mq_quant_fault": (_i32, [C.POINTER(C.c_uint)]),

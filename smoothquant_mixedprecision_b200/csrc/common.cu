@@ -23,7 +23,7 @@ static MqOption g_options[] = {
     {"gemm_bn", {0}},       {"gemm_stages", {0}}, {"quant_rows_per_stage", {0}}, {"quant_warps", {0}},
     {"gemm_persistent", {0}}, {"quant_exact_div", {0}}, {"gemm_debug", {0}}, {"quant_force_generic", {0}},
     {"gemm_profile", {0}}, {"gemm_kernel", {0}}, {"gemm_pair", {0}}, {"gemm_magic_mma", {0}},
-    {"quant_h2", {0}},
+    {"quant_h2", {0}}, {"decode_bps", {0}}, {"decode_tpc", {0}}, {"decode_split", {0}},
 };
 
 int mq_get_option(const char* name, int dflt) {

@@ -455,7 +455,8 @@ class W4A4Linear(nn.Module):
         ks = 0 if self.sal_sorted is None else self.sal_sorted.numel()
         wq = ops.QuantizedRows(codes=self.w_codes, scales=self.w_scales, sal=self.w_sal, rows=self.out_features,
                                Kn=self.perm.numel(), Ks=ks, group_size=self.group_size, int_groups=G, n_salient=ks)
-        self.w_decode = ops.pack_decode(wq)
+        self.w_decode = ops.pack_decode(wq, self.w_sal.dtype if self.w_sal is not None else (
+            self.bias.dtype if self.bias is not None and self.bias.dtype in (torch.float16, torch.bfloat16) else torch.float16))
         if not keep_prefill:
             self.w_codes = None
             self.w_sal = None
@@ -470,7 +471,8 @@ class W4A4Linear(nn.Module):
             raise RuntimeError("layer holds neither prefill codes nor a decode layout")
         N, G, g = self.out_features, d.groups, d.group_size
         tiles = (N + 15) // 16
-        nib = d.nib.view(tiles, -1, 8, 4, 2, 2, 4)                          # [tile, unit, gid, tq, pk, pr, j]
+        rec = d.record_bytes                                                # per (tile, block): nibbles, then scales
+        nib = d.nib.view(tiles, -1, rec)[:, :, :2048].reshape(tiles, -1, 8, 4, 2, 2, 4)   # [tile, unit, gid, tq, pk, pr, j]
         units = nib.shape[1]
         both = torch.stack(((nib & 15), (nib >> 4)), dim=-1).to(torch.int8)  # [..., j, hl]: low nibble k, high k + 32
         both = ((both ^ 8) - 8)                                              # two's-complement nibble -> int8

@@ -306,10 +306,10 @@ DECODE_EVENTS = None        # set to a list to collect (start_event, end_event, 
 
 @dataclass
 class DecodeWeights:
-    """INT4-resident weight operand of the decode kernel (mq_pack_decode layout)."""
-    nib: torch.Tensor              # uint8 [tiles * blocks * 2048]   two codes per byte
-    sal: Optional[torch.Tensor]    # uint8 [tiles * sal_blocks * 2048] salient slice (16-bit values), mma fragment order
-    scales: torch.Tensor           # fp32  [G, ld_ws] group-major (shared with the prefill operand)
+    """INT4-resident weight operand of the decode kernel (mq_pack_decode layout; the group scales travel inside the
+    nibble stream, in the compute dtype)."""
+    nib: torch.Tensor              # uint8: per (row tile, 256-column block) 2048 B of nibbles + the block's scales
+    sal: Optional[torch.Tensor]    # uint8: salient slice (16-bit values) in mma fragment order
     rows: int
     groups: int
     group_size: int
@@ -317,20 +317,25 @@ class DecodeWeights:
     dtype: torch.dtype
 
     def nbytes(self) -> int:
-        return self.nib.numel() + (0 if self.sal is None else self.sal.numel()) + self.scales.numel() * 4
+        return self.nib.numel() + (0 if self.sal is None else self.sal.numel())
+
+    @property
+    def record_bytes(self) -> int:
+        return 2048 + 32 * max(1, 256 // self.group_size)
 
 
 def decode_supported(group_size: int, int_groups: Optional[int], groups: int, n_bits: int) -> bool:
-    return group_size >= 64 and group_size % 64 == 0 and groups >= 1 and (int_groups is None or int_groups == groups) \
-        and n_bits <= 4
+    return group_size >= 64 and (group_size & (group_size - 1)) == 0 and groups >= 1 \
+        and (int_groups is None or int_groups == groups) and n_bits <= 4
 
 
-def pack_decode(w: QuantizedRows) -> DecodeWeights:
-    """int8 codes [N, ld] + salient [N, ld_sal] of the prefill operand -> the nibble layout the decode kernel streams."""
+def pack_decode(w: QuantizedRows, dtype: Optional[torch.dtype] = None) -> DecodeWeights:
+    """int8 codes [N, ld] + fp32 group scales + salient [N, ld_sal] of the prefill operand -> the stream the decode
+    kernel reads.  ``dtype``: the 16-bit compute dtype (default: that of the salient slice, else float16)."""
     _need_cuda(w.codes, w.sal)
     N, G, g = w.rows, w.groups, w.group_size
     Ks = 0 if w.sal is None else (w.n_salient if w.n_salient is not None else w.Ks)
-    dt = w.sal.dtype if w.sal is not None else torch.float16
+    dt = dtype or (w.sal.dtype if w.sal is not None else torch.float16)
     import ctypes as C
     nb, sb = C.c_size_t(0), C.c_size_t(0)
     _check(lib.mq_decode_weight_bytes(N, G, g, Ks, C.byref(nb), C.byref(sb)), "mq_decode_weight_bytes")
@@ -338,10 +343,10 @@ def pack_decode(w: QuantizedRows) -> DecodeWeights:
     nib = torch.empty(nb.value, dtype=torch.uint8, device=dev)
     sal = torch.empty(sb.value, dtype=torch.uint8, device=dev) if Ks else None
     with torch.cuda.device(dev):
-        check(lib.mq_pack_decode(w.codes.data_ptr(), w.codes.stride(0), _ptr(w.sal) if Ks else None,
-                                 w.sal.stride(0) if Ks else 0, N, G, g, Ks, _DTYPES[dt], nib.data_ptr(), _ptr(sal),
-                                 torch.cuda.current_stream(dev).cuda_stream), "mq_pack_decode")
-    return DecodeWeights(nib=nib, sal=sal, scales=w.scales, rows=N, groups=G, group_size=g, Ks=Ks, dtype=dt)
+        check(lib.mq_pack_decode(w.codes.data_ptr(), w.codes.stride(0), w.scales.data_ptr(), w.scales.stride(0),
+                                 _ptr(w.sal) if Ks else None, w.sal.stride(0) if Ks else 0, N, G, g, Ks, _DTYPES[dt],
+                                 nib.data_ptr(), _ptr(sal), torch.cuda.current_stream(dev).cuda_stream), "mq_pack_decode")
+    return DecodeWeights(nib=nib, sal=sal, rows=N, groups=G, group_size=g, Ks=Ks, dtype=dt)
 
 
 def decode_gemm(a: QuantizedRows, w: DecodeWeights, bias: Optional[torch.Tensor]) -> torch.Tensor:
@@ -365,7 +370,7 @@ def decode_gemm(a: QuantizedRows, w: DecodeWeights, bias: Optional[torch.Tensor]
     with torch.cuda.device(dev):
         check(lib.mq_decode_gemm(a.codes.data_ptr(), a.codes.stride(0), a.scales.data_ptr(), a.scales.stride(0),
                                  _ptr(a.sal) if w.Ks else None, a.sal.stride(0) if w.Ks else 0,
-                                 w.nib.data_ptr(), w.scales.data_ptr(), w.scales.stride(0), _ptr(w.sal), _ptr(bias),
+                                 w.nib.data_ptr(), _ptr(w.sal), _ptr(bias),
                                  M, N, G, g, w.Ks, _DTYPES[dt], y.data_ptr(), y.stride(0),
                                  torch.cuda.current_stream(dev).cuda_stream), "mq_decode_gemm")
     if ev is not None:

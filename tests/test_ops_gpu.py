@@ -457,9 +457,10 @@ def test_decode_gemm_matches_prefill_kernel_and_composed_reference(ops, mqlib, M
     sal = torch.sort(order[:ks]).values.to(DEV) if ks else None
     a = ops.quant_rows(x.to(DEV), perm, sal, g)
     wq = ops.quant_rows(w.to(DEV), perm, sal, g)
-    dw = ops.pack_decode(wq)
+    dw = ops.pack_decode(wq, dtype)
     Kn, G = K - ks, (K - ks + g - 1) // g
-    assert dw.nib.numel() == ((N + 15) // 16) * ((G * g + 255) // 256) * 2048       # 0.5 byte per (padded) weight
+    # 0.5 byte per (padded) weight + one 16-bit scale per (row, group)
+    assert dw.nib.numel() == ((N + 15) // 16) * ((G * g + 255) // 256) * (2048 + 32 * max(1, 256 // g))
     y_dec = ops.decode_gemm(a, dw, bias.to(DEV))
     y_pre = ops.mixed_gemm(a, wq, bias.to(DEV))
     torch.cuda.synchronize()
@@ -470,8 +471,41 @@ def test_decode_gemm_matches_prefill_kernel_and_composed_reference(ops, mqlib, M
     assert float((y_dec.double() - ref).abs().max()) <= tol
     ulp = 2.0 ** (-7 if dtype == torch.bfloat16 else -10)
     assert float((y_dec.float() - y_pre.float()).abs().max()) <= 2 * ulp * scale
-    if ks == 0:
-        assert torch.equal(y_dec, y_pre)          # integer part: bit-identical to the prefill kernel
+    if ks == 0:                                   # integer part without split-K: bit-identical to the prefill kernel
+        mqlib.set_option("decode_split", 1)
+        try:
+            assert torch.equal(ops.decode_gemm(a, dw, bias.to(DEV)), y_pre)
+        finally:
+            mqlib.set_option("decode_split", 0)
+
+
+@pytest.mark.parametrize("split,tpc", [(2, 0), (4, 0), (8, 0), (1, 3), (4, 5)])
+@pytest.mark.parametrize("M,N,K,g,p", [(16, 1024, 8192, 128, 0.1), (7, 520, 4096, 1024, 0.05), (40, 2048, 2048, 64, 0.0)])
+def test_decode_gemm_split_k_is_deterministic_and_exact(ops, mqlib, M, N, K, g, p, split, tpc):
+    """Cluster split-K (decode_split CTAs share the row tiles and cut K on group boundaries, partial tiles summed in rank
+    order through the leader's shared memory) against the fp64 composition; two runs are bit-identical."""
+    x = synth(M, K, torch.float16, seed=M)
+    gen = torch.Generator().manual_seed(K)
+    w = (torch.randn(N, K, generator=gen) * 0.05).half()
+    order = torch.randperm(K, generator=gen)
+    ks = int(p * K)
+    perm = order[ks:].to(DEV)
+    sal = torch.sort(order[:ks]).values.to(DEV) if ks else None
+    a = ops.quant_rows(x.to(DEV), perm, sal, g)
+    wq = ops.quant_rows(w.to(DEV), perm, sal, g)
+    dw = ops.pack_decode(wq, torch.float16)
+    mqlib.set_option("decode_split", split)
+    mqlib.set_option("decode_tpc", tpc)
+    try:
+        y1 = ops.decode_gemm(a, dw, None).clone()
+        y2 = ops.decode_gemm(a, dw, None)
+        torch.cuda.synchronize()
+    finally:
+        mqlib.set_option("decode_split", 0)
+        mqlib.set_option("decode_tpc", 0)
+    assert torch.equal(y1, y2)
+    ref = _gemm_reference(a, wq, None, ks, M, N).double()
+    assert float((y1.double() - ref).abs().max()) <= 1e-3 * float(ref.abs().max()) + 1e-3
 
 
 def test_decode_layer_releases_prefill_codes_and_rebuilds_them(ops):
