@@ -4,7 +4,9 @@ Workload (one "step"): every W4A4 linear of Llama-2-7B (32 decoder layers x {q,k
 group 128, 5 % salient FP16 channels, static max-sort permutation, mode="fused") applied to one batch of 16 x 2048 =
 32 768 tokens per GPU, chained through their real shapes (x -> q,k,v ; v -> o ; o -> gate,up ; up -> down -> next
 layer).  Attention / norms / lm_head are not part of the path and are not executed.  Synthetic fp16 activations and
-random-init weights.  N > 1: one replica per GPU, data-parallel over sequences, no data-path collective ("weak").
+random-init weights.  N > 1: the HEADLINE is column-parallel (ONE 32 768-token batch, the 224 linears sharded over
+out_features, "strong"); the data-parallel figure (one replica per GPU, no collective, "weak") is the `data_parallel`
+sub-record.  `--parallel dp|tp` measures one of them alone.
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
 
@@ -17,8 +19,10 @@ random-init weights.  N > 1: one replica per GPU, data-parallel over sequences, 
           with stock PyTorch CUDA ops, and plain fp16 F.linear, over one decoder layer's 7 linears at the full 32 768
           tokens on the same GPU (x 32 layers): the like-for-like GPU baselines of SURVEY 8(d)
 `gemm_tops` (N = 1) the isolated mixed GEMM at the three Llama-2-7B linear shapes, M = 32 768
-`column_parallel` (N > 1) the same 224 linears sharded over out_features across the N GPUs (strong scaling of ONE
-          32 768-token batch, NCCL all-gathers where the consumer needs the full width), with the comm / compute split
+`column_parallel` (N > 1) comm / compute split of the headline: NCCL rank count, bytes received per rank, the step
+          with every gather serialised (CUDA events around each collective) vs overlapped, the limiting collective
+          with its bytes and GB/s
+`decode`  (N = 1) config 5: mq_decode_gemm from INT4-resident weights at the Llama-2-70B / 7B linear shapes, M = 1, 16
 `--impl reference` times that CPU path alone (all host threads) and prints the same line with "impl": "reference".
 """
 import argparse
@@ -56,9 +60,14 @@ def parse():
     ap.add_argument("--cpu-layers", type=int, default=2, help="decoder layers of the bounded CPU sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-gpu-baselines", action="store_true")
-    ap.add_argument("--parallel", default="dp", choices=["dp", "tp"],
-                    help="N > 1: dp = one replica per GPU over different sequences (weak scaling, no collective); "
-                         "tp = column-parallel over out_features with NCCL all-gathers (strong scaling)")
+    ap.add_argument("--parallel", default="auto", choices=["auto", "dp", "tp"],
+                    help="N > 1: tp = column-parallel over out_features with NCCL all-gathers (strong scaling of one "
+                         "batch); dp = one replica per GPU over different sequences (weak scaling, no collective); "
+                         "auto = tp as the headline with the dp figure as the `data_parallel` sub-record")
+    ap.add_argument("--tp-chunks", type=int, default=2,
+                    help="tp: row chunks of the batch pipelined through the layers so that one chunk's all-gather "
+                         "overlaps the other chunk's GEMM")
+    ap.add_argument("--no-decode", action="store_true")
     return ap.parse_args()
 
 
@@ -311,10 +320,30 @@ def build_stack(layers, tokens, dev, seed, tp=None):
         fold_mlp_permutation(mods["gate_proj"], mods["up_proj"], mods["down_proj"])
         if tp is not None:            # column-parallel: gather only where the consumer needs the full width
             for name in mods:
-                mods[name].shard_(tp[0], tp[1], gather_output=dict(PLAN)[name])
+                mods[name].shard_(tp[0], tp[1], gather_output=dict(PLAN)[name], blocked_output=True)
         stack.append(mods)
     x0 = (torch.randn(tokens, HIDDEN, device=dev, generator=g) * chan[HIDDEN]).half()
     return stack, x0
+
+
+def run_stack_tp(stack, xs):
+    """Column-parallel pass over row chunks `xs` of the batch.  Gathered layers (v, o, up, down) return
+    parallel.BlockedColumns whose all-gather is still in flight; the collective of one chunk overlaps the GEMMs issued
+    after it (the column-local q / k / gate of the same chunk and everything of the other chunk), and the consumer's
+    row quantiser reads the gathered [p, M, S] buffer in place."""
+    for m in stack:
+        vs = []
+        for x in xs:
+            vs.append(m["v_proj"](x))
+            m["q_proj"](x)
+            m["k_proj"](x)
+        os_ = [m["o_proj"](v) for v in vs]
+        us = []
+        for o in os_:
+            us.append(m["up_proj"](o))
+            m["gate_proj"](o)
+        xs = [m["down_proj"](u) for u in us]
+    return xs
 
 
 def run_stack(stack, x):
@@ -343,12 +372,10 @@ def gpu_arm(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     M = args.tokens
-    tp = args.parallel == "tp" and world > 1
-    stack, x0 = build_stack(args.layers, M, dev, seed=1234 + (0 if tp else rank), tp=(rank, world) if tp else None)
-    job_tokens = M if tp else world * M
-    hx = torch.empty(x0.shape, dtype=x0.dtype, pin_memory=True).copy_(x0)
-    hy = torch.empty(x0.shape, dtype=x0.dtype, pin_memory=True)
-    xd = torch.empty_like(x0)
+    mode = args.parallel
+    if mode == "auto":
+        mode = "tp" if world > 1 else "dp"
+    tp = mode == "tp" and world > 1
 
     def sync_all():
         if world > 1:
@@ -368,33 +395,103 @@ def gpu_arm(args):
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item()) / steps
 
-    def step_resident():
-        run_stack(stack, x0)
+    def measure(stack, x0, use_tp, clocks_on):
+        """resident + e2e timing of one stack; returns the numbers of the JSON line"""
+        hx = torch.empty(x0.shape, dtype=x0.dtype, pin_memory=True).copy_(x0)
+        hy = torch.empty(x0.shape, dtype=x0.dtype, pin_memory=True)
+        xd = torch.empty_like(x0)
+        nch = max(1, args.tp_chunks) if use_tp else 1
+        rows = [(i * M // nch, (i + 1) * M // nch) for i in range(nch)]
 
-    def step_e2e():
-        xd.copy_(hx, non_blocking=True)
-        y = run_stack(stack, xd)
-        hy.copy_(y, non_blocking=True)
-        torch.cuda.current_stream().synchronize()      # the caller holds the result on the host
+        def run(x):
+            if not use_tp:
+                return run_stack(stack, x)
+            outs = run_stack_tp(stack, [x[a:b] for a, b in rows])
+            return outs
 
-    for _ in range(max(3, args.warmup)):
-        step_resident()
-    c0 = ops.COUNTERS["launch_calls"]
-    ops.GEMM_EVENTS = []
-    ops.QUANT_EVENTS = []
-    sampler = ClockSampler(local) if rank == 0 else None
-    ms = timed(step_resident, args.steps)
-    clocks = sampler.stop() if sampler else None
-    launches = (ops.COUNTERS["launch_calls"] - c0) // args.steps
-    ev, ops.GEMM_EVENTS = ops.GEMM_EVENTS, None
-    qev, ops.QUANT_EVENTS = ops.QUANT_EVENTS, None
-    quant_ms = sum(a.elapsed_time(b) for a, b, _ in qev) / args.steps
-    quant_bytes = sum(e[2] for e in qev) / args.steps
-    gemm_ms = sum(a.elapsed_time(b) for a, b, _, _ in ev) / args.steps
-    ops_i8 = sum(e[2] for e in ev) / args.steps
-    ops_f16 = sum(e[3] for e in ev) / args.steps
-    step_e2e()
-    ms_e2e = timed(step_e2e, args.steps)
+        def step_resident():
+            run(x0)
+
+        def step_e2e():
+            xd.copy_(hx, non_blocking=True)
+            y = run(xd)
+            if use_tp:
+                for (a, b), yc in zip(rows, y):
+                    hy[a:b].copy_(yc.dense() if hasattr(yc, "dense") else yc, non_blocking=True)
+            else:
+                hy.copy_(y, non_blocking=True)
+            torch.cuda.current_stream().synchronize()      # the caller holds the result on the host
+
+        for _ in range(max(3, args.warmup)):
+            step_resident()
+        c0 = ops.COUNTERS["launch_calls"]
+        ops.GEMM_EVENTS, ops.QUANT_EVENTS = [], []
+        sampler = ClockSampler(local) if (rank == 0 and clocks_on) else None
+        ms = timed(step_resident, args.steps)
+        clocks = sampler.stop() if sampler else None
+        r = {"ms": ms, "clocks": clocks, "launches": (ops.COUNTERS["launch_calls"] - c0) // args.steps}
+        ev, ops.GEMM_EVENTS = ops.GEMM_EVENTS, None
+        qev, ops.QUANT_EVENTS = ops.QUANT_EVENTS, None
+        r["quant_ms"] = sum(a.elapsed_time(b) for a, b, _ in qev) / args.steps
+        r["quant_bytes"] = sum(e[2] for e in qev) / args.steps
+        r["quant_launches"] = len(qev) // args.steps
+        r["gemm_ms"] = sum(a.elapsed_time(b) for a, b, _, _ in ev) / args.steps
+        r["ops_i8"] = sum(e[2] for e in ev) / args.steps
+        r["ops_f16"] = sum(e[3] for e in ev) / args.steps
+        r["gemm_launches"] = len(ev) // args.steps
+        step_e2e()
+        r["ms_e2e"] = timed(step_e2e, args.steps)
+        r["h2d"], r["d2h"] = hx.numel() * 2, hy.numel() * 2
+        if use_tp:
+            # comm / compute split: the same step with every gather serialised behind its GEMM and timed on the
+            # stream (CUDA events around the blocking collective), max over ranks of the per-step totals
+            from smoothquant_mixedprecision_b200 import parallel as par
+            par.ASYNC_GATHER, par.COMM_EVENTS = False, []
+            ops.GEMM_EVENTS, ops.QUANT_EVENTS = [], []
+            step_resident()
+            par.COMM_EVENTS, ops.GEMM_EVENTS, ops.QUANT_EVENTS = [], [], []
+            ms_serial = timed(step_resident, args.steps)
+            cev, par.COMM_EVENTS, par.ASYNC_GATHER = par.COMM_EVENTS, None, True
+            gev, ops.GEMM_EVENTS = ops.GEMM_EVENTS, None
+            kev, ops.QUANT_EVENTS = ops.QUANT_EVENTS, None
+            by_bytes = {}
+            for a, b, nbytes in cev:
+                d = by_bytes.setdefault(nbytes, [0.0, 0])
+                d[0] += a.elapsed_time(b)
+                d[1] += 1
+            comm_ms = sum(v[0] for v in by_bytes.values()) / args.steps
+            t = torch.tensor([comm_ms, sum(a.elapsed_time(b) for a, b, _, _ in gev) / args.steps,
+                              sum(a.elapsed_time(b) for a, b, _ in kev) / args.steps], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            worst = max(by_bytes.items(), key=lambda kv: kv[1][0])
+            per_call_ms = worst[1][0] / worst[1][1]
+            r["comm"] = {
+                "nccl_ranks": world, "nccl_version": ".".join(str(v) for v in torch.cuda.nccl.version()),
+                "collectives_per_step": len(cev) // args.steps, "row_chunks": nch,
+                "bytes_received_per_rank_per_step": sum(k * v[1] for k, v in by_bytes.items()) // args.steps,
+                "serialised": {"ms_per_step": ms_serial, "comm_ms": float(t[0]), "gemm_ms": float(t[1]),
+                               "quantiser_ms": float(t[2])},
+                "overlapped": {"ms_per_step": ms, "exposed_comm_ms": max(0.0, ms - (ms_serial - float(t[0])))},
+                "limiting_collective": {
+                    "what": "all_gather_into_tensor of one row chunk of a gathered layer output "
+                            f"([{world}, {rows[0][1] - rows[0][0]}, S] fp16, in place)",
+                    "bytes_received_per_rank": worst[0], "calls_per_step": worst[1][1] // args.steps,
+                    "ms_per_call": per_call_ms, "algbw_GBs": worst[0] / per_call_ms / 1e6,
+                    "busbw_note": "bytes received per rank / time: (p-1)/p of the gathered tensor over NVLink"}}
+        return r
+
+    stack, x0 = build_stack(args.layers, M, dev, seed=1234 + (0 if tp else rank), tp=(rank, world) if tp else None)
+    job_tokens = M if tp else world * M
+    main = measure(stack, x0, tp, True)
+    other = None
+    if world > 1 and args.parallel == "auto":           # the data-parallel figure beside the column-parallel headline
+        del stack
+        torch.cuda.empty_cache()
+        stack, x0 = build_stack(args.layers, M, dev, seed=1234 + rank, tp=None)
+        other = measure(stack, x0, False, False)
+    ms, ms_e2e, clocks, launches = main["ms"], main["ms_e2e"], main["clocks"], main["launches"]
+    quant_ms, quant_bytes, gemm_ms = main["quant_ms"], main["quant_bytes"], main["gemm_ms"]
+    ops_i8, ops_f16 = main["ops_i8"], main["ops_f16"]
     fault = _lib.gemm_fault()[0] or _lib.quant_fault()[0]
     if fault:
         raise SystemExit(f"bench.py: kernel fault record {fault:#x}")
@@ -437,29 +534,40 @@ def gpu_arm(args):
             "data": "synthetic",
             "config": {"workload": "Llama-2-7B W4A4 linears (224 layers), g=128, 5% salient FP16, static max-sort, "
                                    "prefill 16x2048 tokens per GPU (dp) or per job (tp)", "tokens_per_gpu": M, "layers": args.layers,
-                       "group_size": GROUP, "salient_prop": SALIENT, "parallelism": f"tp{world} (column-parallel, NCCL all-gather of v/o/up/down outputs)" if tp
+                       "group_size": GROUP, "salient_prop": SALIENT,
+                       "parallelism": (f"tp{world}: column-parallel over out_features, ONE {M}-token batch per job; "
+                                       "v/o/up/down outputs all-gathered in place into [p, M, S] (NCCL, async, "
+                                       f"{max(1, args.tp_chunks)} row chunks) and quantised from that layout") if tp
                        else f"dp{world}",
                        "l2": "inputs (268 MB activations, 6.9 GB weights) exceed the 126 MB L2; no flush"},
             "tops": job_tokens * ops_per_token(args.layers) / (ms * 1e-3) / 1e12,
-            "e2e": {"value": job_tokens / (ms_e2e * 1e-3), "unit": "tokens/s", "h2d_bytes_per_step": hx.numel() * 2,
-                    "d2h_bytes_per_step": hy.numel() * 2, "ms_per_step": ms_e2e},
+            "e2e": {"value": job_tokens / (ms_e2e * 1e-3), "unit": "tokens/s", "h2d_bytes_per_step": main["h2d"],
+                    "d2h_bytes_per_step": main["d2h"], "ms_per_step": ms_e2e},
             "gpu_launches": launches,
             "roofline": {"kernel": "mixed_gemm_kernel", "bound": "tensor", "achieved": achieved, "peak": peak_mix,
                          "unit": "TOP/s", "frac": achieved / peak_mix, "traffic": traffic.get("mixed_gemm_kernel"),
                          "traffic_unit": "DRAM bytes per launch (ncu, profiles/*_traffic.json)", "peak_source": peak_src,
-                         "share_of_step": gemm_ms / ms, "launches_per_step": len(ev) // args.steps,
+                         "share_of_step": gemm_ms / ms, "launches_per_step": main["gemm_launches"],
                          "fractions": fractions,
                          "ops_note": "ops = 2*M*N*Kn on the int8 pipe (true quantised columns, no padding) + 2*M*N*Ks "
                                      "on the f16 pipe"},
-            "roofline_quantiser": {"kernel": "quant_rows_fast", "bound": "hbm",
+            "roofline_quantiser": {"kernel": "quant_rows_h2", "bound": "hbm",
                                    "achieved": quant_bytes / (quant_ms * 1e-3) / 1e9,
                                    "peak": peaks.get("hbm_gbs") or 6500.0, "unit": "GB/s",
                                    "frac": quant_bytes / (quant_ms * 1e-3) / 1e9 / (peaks.get("hbm_gbs") or 6500.0),
-                                   "traffic": traffic.get("quant_rows_fast"),
-                                   "algorithmic_bytes_per_launch": quant_bytes / max(1, len(qev) // args.steps),
+                                   "traffic": traffic.get("quant_rows_h2", traffic.get("quant_rows_fast")),
+                                   "algorithmic_bytes_per_launch": quant_bytes / max(1, main["quant_launches"]),
                                    "share_of_step": quant_ms / ms,
-                                   "launches_per_step": len(qev) // args.steps},
+                                   "launches_per_step": main["quant_launches"]},
             "clocks": clocks}
+    if tp:
+        line["column_parallel"] = main["comm"]
+    if other is not None:
+        line["data_parallel"] = {
+            "value": world * M / (other["ms"] * 1e-3), "unit": "tokens/s", "scaling": "weak",
+            "ms_per_step": other["ms"], "tokens_per_gpu": M,
+            "e2e": {"value": world * M / (other["ms_e2e"] * 1e-3), "unit": "tokens/s"},
+            "what": f"one replica per GPU over different sequences, no data-path collective (dp{world})"}
     if world == 1 and not args.no_gpu_baselines:
         xk = {HIDDEN: x0, INTER: torch.randn(M, INTER, device=dev, dtype=torch.float16)}
         line["gemm_tops"] = isolated_gemm_tops(stack[0], xk)
@@ -472,6 +580,22 @@ def gpu_arm(args):
         line["fp16_cublas"] = {
             "value": M / (t_fp16 * LAYERS), "unit": "tokens/s", "ms_per_decoder_layer": t_fp16 * 1e3,
             "what": "plain fp16 F.linear (cuBLAS) on the same 7 shapes x 32768 tokens, x 32"}
+    if world == 1 and not args.no_decode:
+        # config 5 (decode regime): mq_decode_gemm from INT4-resident weights, CUDA-graph replay over operand copies
+        # larger than L2 (tools/decode_time.py); bytes = int4 weights + scales + salient slice + activations + y
+        del stack
+        torch.cuda.empty_cache()
+        sys.path.insert(0, os.path.join(ROOT, "tools"))
+        import decode_time
+        hbm = peaks.get("hbm_gbs") or 6500.0
+        line["decode"] = {
+            "what": "one linear, M tokens, g=128, 10% salient, weights INT4-resident (4 bits per non-salient weight); "
+                    "us per call, achieved GB/s on the bytes the call must move, fraction of the measured HBM peak; "
+                    "us_prefill_kernel = the tcgen05 prefill kernel on the same shape (int8-resident codes)",
+            "hbm_peak_GBs": hbm,
+            "points": [dict(shape=r["shape"], N=r["N"], K=r["K"], M=r["M"], us=round(r["us_decode"], 2),
+                            us_prefill_kernel=round(r["us_prefill_kernel"], 2), GBs=round(r["gbs"], 1),
+                            frac_hbm=round(r["gbs"] / hbm, 3)) for r in decode_time.measure([1, 16])]}
     if world == 1 and not args.no_cpu_baseline:
         r = time_cpu(args.cpu_tokens, 2, 1, args.cpu_layers)
         line["cpu_baseline"] = {"value": r["tok_s"], "unit": "tokens/s", "cores": r["threads"], "kind": "port",

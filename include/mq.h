@@ -104,6 +104,21 @@ int mq_quant_rows_split(const void* x, int64_t R, int64_t K, int64_t ld, int dty
                         int8_t* out_codes, int64_t ld_codes, float* out_scales, int64_t ld_scales,
                         void* out_sal, int64_t ld_sal, void* stream);
 
+/* mq_quant_rows on a column-BLOCKED input: the K columns of a row live in x_blocks blocks of blk_cols columns
+ * (the last one may be narrower), block b at x + b * blk_stride elements, rows of a block `ld` elements apart --
+ * [x_blocks][R][blk_cols] is what an all-gather of the column shards of a column-parallel producer leaves behind
+ * (torch.distributed.all_gather_into_tensor; the reference has no tensor parallelism, its
+ * F.linear -> quantize_activation_per_group_absmax chain, fake_quant.py:306 -> :78-101, sees a dense tensor).  The
+ * kernel's bulk copies reassemble every row in shared memory, so the gathered activations are never re-laid-out
+ * in HBM.  Results are bit-identical to mq_quant_rows on the dense tensor.  16-bit dtypes, power-of-two group
+ * sizes 32..1024, blk_cols % 8 == 0, blk_stride % 8 == 0, no smoothing divisor; anything else returns
+ * MQ_ERR_UNSUPPORTED (gather into a dense tensor and call mq_quant_rows).  x_blocks == 1 is mq_quant_rows. */
+int mq_quant_rows_blocked(const void* x, int64_t R, int64_t K, int x_blocks, int64_t blk_cols, int64_t blk_stride,
+                          int64_t ld, int dtype, const int32_t* perm, int64_t Kn, const int32_t* sal, int64_t Ks,
+                          int group_size, int n_bits,
+                          int8_t* out_codes, int64_t ld_codes, float* out_scales, int64_t ld_scales,
+                          void* out_sal, int64_t ld_sal, void* stream);
+
 /* Same arithmetic, reference-shaped output: out [R, K] (dtype) holds code*scale at the ORIGINAL column of every
  * permuted position and x itself at every column not listed in perm (salient pass-through).
  *     Replaces  quantize_activation_per_group_absmax_sort   fake_quant.py:105-154  (perm = argsort of the key)

@@ -369,6 +369,8 @@ class W4A4Linear(nn.Module):
 
     @torch.no_grad()
     def forward(self, x, act_perm=None, out_perm=None):
+        if isinstance(x, parallel.BlockedColumns):      # gathered output of a column-parallel producer, [p, M, S]
+            return self._forward_blocked_input(x)
         shape = x.shape
         if x.dim() == 3:
             x2 = x.reshape(-1, shape[-1])
@@ -379,6 +381,8 @@ class W4A4Linear(nn.Module):
         if act_perm is not None or out_perm is not None:               # parity replay of a recorded permutation
             _validate_columns(act_perm, self.in_features, "act_perm")
             _validate_columns(out_perm, self.full_out_features, "out_perm")
+        if self._emits_blocked() and x.dim() == 2:
+            return self._forward_fused(x, x2, blocked_out=True)
         if self.mode == "fused":
             y = self._forward_fused(x, x2)
         else:
@@ -391,12 +395,35 @@ class W4A4Linear(nn.Module):
             y = y.to(x2.dtype)
         return y.view(shape[0], shape[1], -1) if x.dim() == 3 else y
 
+    def _emits_blocked(self):
+        return (self.tp_world > 1 and self.tp_gather_output and getattr(self, "tp_blocked_output", False)
+                and self.mode == "fused" and self.output_quant_name == "None")
+
+    def _forward_blocked_input(self, xb):
+        """x arrives as parallel.BlockedColumns: K1 reads the gather layout in place (mq_quant_rows_blocked); layers
+        or shapes it does not cover take the dense view."""
+        if xb.n_cols != self.in_features:
+            raise ValueError(f"blocked input has {xb.n_cols} columns, layer wants {self.in_features}")
+        cdt = self.w_sal.dtype if self.w_sal is not None else (
+            self.w_decode.dtype if self.w_decode is not None else xb.dtype)
+        G = 0 if self.perm is None else (self.perm.numel() + self.group_size - 1) // self.group_size
+        g = self.group_size
+        ok = (self.mode == "fused" and xb.dtype == cdt and xb.buf.shape[0] > 1 and xb.buf.shape[2] % 8 == 0
+              and (self.int_groups is None or self.int_groups == G) and G >= 1 and 32 <= g <= 1024 and g & (g - 1) == 0
+              and self.in_features % 8 == 0 and self.quant_bits <= (8 if cdt == torch.float16 else 7))
+        if not ok:
+            return self.forward(xb.dense())
+        return self._forward_fused(xb, xb, blocked_out=self._emits_blocked())
+
     # ---- column-parallel sharding over out_features (SURVEY 8(e)); no reference counterpart
     @torch.no_grad()
-    def shard_(self, rank, world, group=None, gather_output=True):
+    def shard_(self, rank, world, group=None, gather_output=True, blocked_output=False):
         """Keep only the output columns that ``rank`` of ``world`` owns (rows of the packed weight / scales / salient
         slice / bias).  With ``gather_output`` the forward all-gathers y back to the full width over ``group``;
-        without it the layer returns its [M, N_local] column block (consumer is column-local)."""
+        without it the layer returns its [M, N_local] column block (consumer is column-local).  ``blocked_output``
+        (mode="fused", 2-D inputs): the gathered output is returned as a parallel.BlockedColumns -- the GEMM writes its
+        own block of the [world, M, S] gather buffer, the all-gather runs in place and asynchronously, and the next
+        W4A4Linear quantises straight from that layout; call ``.dense()`` on it for any other consumer."""
         if self.tp_world != 1:
             raise RuntimeError("layer is already sharded")
         if self.w_decode is not None:
@@ -420,22 +447,35 @@ class W4A4Linear(nn.Module):
         self.full_out_features = N
         self.out_features = hi - lo
         self.tp_rank, self.tp_world, self.tp_group, self.tp_gather_output = rank, world, group, gather_output
+        self.tp_blocked_output = bool(blocked_output)
         return self
 
-    def _forward_fused(self, x, x2):
+    def _forward_fused(self, x, x2, blocked_out=False):
         cdt = self.w_sal.dtype if self.w_sal is not None else (self.w_decode.dtype if self.w_decode is not None else (
             x2.dtype if x2.dtype in (torch.float16, torch.bfloat16) else torch.float16))
         xin = x2 if x2.dtype == cdt else x2.to(cdt)
+        if blocked_out:
+            # the GEMM writes this rank's block of the gather buffer; the collective then runs in place and async
+            buf = parallel.gather_buffer(x2.shape[0], self.full_out_features, self.tp_world, cdt, x2.device)
+            y = self._fused_gemm(x, xin, cdt, out=buf[self.tp_rank])
+            return parallel.gather_columns_blocked(buf[self.tp_rank][:, : y.shape[1]], self.full_out_features,
+                                                   self.tp_group, buf=buf)
+        return self._fused_gemm(x, xin, cdt)
+
+    def _fused_gemm(self, x, xin, cdt, out=None):
         # layers fed by the same tensor with the same K partition (q/k/v, gate/up: same calibration statistics in
         # the reference, fake_quant.py:396-455) share one quantised activation
         a = _shared_act(x, xin, self)
-        if self.w_decode is not None and a.rows <= ops.DECODE_MAX_TOKENS:
-            return ops.decode_gemm(a, self.w_decode, self.bias)      # weight-bandwidth regime: int4-resident weights
+        # weight-bandwidth regime: int4-resident weights.  Up to DECODE_PREFER_TOKENS the decode kernel wins outright;
+        # between that and DECODE_MAX_TOKENS it is only taken when the prefill operand is not resident
+        if self.w_decode is not None and (a.rows <= ops.DECODE_PREFER_TOKENS or (
+                self.w_codes is None and a.rows <= ops.DECODE_MAX_TOKENS)):
+            return ops.decode_gemm(a, self.w_decode, self.bias, out=out)
         if self.w_codes is None:
             self._restore_prefill_operand()          # stays resident from now on: the layer serves both regimes
         w = ops.QuantizedRows(codes=self.w_codes, scales=self.w_scales, sal=self.w_sal, rows=self.out_features,
                               Kn=a.Kn, Ks=a.Ks, group_size=self.group_size, int_groups=a.int_groups)
-        return ops.mixed_gemm(a, w, self.bias, out_dtype=cdt)
+        return ops.mixed_gemm(a, w, self.bias, out_dtype=cdt, out=out)
 
     # ---- decode regime: INT4-resident weights (BASELINE config 5; no reference counterpart beyond F.linear :306)
     @torch.no_grad()
@@ -457,9 +497,10 @@ class W4A4Linear(nn.Module):
                                Kn=self.perm.numel(), Ks=ks, group_size=self.group_size, int_groups=G, n_salient=ks)
         self.w_decode = ops.pack_decode(wq, self.w_sal.dtype if self.w_sal is not None else (
             self.bias.dtype if self.bias is not None and self.bias.dtype in (torch.float16, torch.bfloat16) else torch.float16))
-        if not keep_prefill:
+        if not keep_prefill:                # the group scales travel inside the nibble stream: nothing else stays
             self.w_codes = None
             self.w_sal = None
+            self.w_scales = None
         return self
 
     def _restore_prefill_operand(self):
@@ -488,6 +529,16 @@ class W4A4Linear(nn.Module):
             ws = torch.zeros((N, (d.Ks + 7) // 8 * 8), dtype=d.dtype, device=d.nib.device)
             ws[:, : d.Ks] = rows[:, : d.Ks]
             self.w_sal = ws
+        if self.w_scales is None:           # fp32 group-major table from the scale slots behind every record's nibbles
+            slots = (rec - 2048) // 32
+            sc = d.nib.view(tiles, -1, rec)[:, :, 2048:].contiguous().view(d.dtype).view(tiles, -1, slots, 16)
+            if g >= 256:                    # one slot per block, a group spans g / 256 blocks: take its first block
+                tab = sc[:, :: g // 256, 0, :].permute(1, 0, 2).reshape(-1, tiles * 16)
+            else:                           # block b, slot s holds group b * (256 / g) + s
+                tab = sc.permute(1, 2, 0, 3).reshape(-1, tiles * 16)
+            full = torch.zeros((max(G, 1), max((N + 3) // 4 * 4, 4)), dtype=torch.float32, device=d.nib.device)
+            full[:G, :N] = tab[:G, :N].float()
+            self.w_scales = full
 
     def device_weight_bytes(self) -> int:
         """Bytes this layer's weight operands occupy on the device right now (all resident copies)."""
@@ -606,6 +657,7 @@ class W4A4Linear(nn.Module):
             if released:
                 self.w_codes = None
                 self.w_sal = None
+                self.w_scales = None
 
     def _dequantized_weight(self):
         N, K, g = self.out_features, self.in_features, self.group_size

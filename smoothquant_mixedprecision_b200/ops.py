@@ -130,9 +130,20 @@ def quant_rows(x: torch.Tensor, perm: Optional[torch.Tensor], sal: Optional[torc
     perm=None means the identity over the first Kn columns (fake_quant.py:78-101 / :30-53 on x[:, perm]).
     ``int_groups`` < G (hybrid engine): only the first ``int_groups`` groups leave as codes, the rest leave
     dequantised behind the salient columns of ``sal`` (mq_quant_rows_split)."""
-    _need_cuda(x, perm, sal, smooth)
-    x2 = _rows2d(x)
-    R, K = x2.shape
+    blocked = hasattr(x, "buf") and hasattr(x, "n_cols")      # parallel.BlockedColumns: [world, M, S] gather layout
+    if blocked:
+        bc, x = x, x.buf
+        bc.wait()
+        _need_cuda(x, perm, sal, smooth)
+        if smooth is not None:
+            raise ValueError("a blocked input takes no smoothing divisor; call .dense() first")
+        x2 = x
+        nb, R, S = x2.shape
+        K = bc.n_cols
+    else:
+        _need_cuda(x, perm, sal, smooth)
+        x2 = _rows2d(x)
+        R, K = x2.shape
     dev = x.device
     perm = _i32(perm, dev)
     sal = _i32(sal, dev)
@@ -145,6 +156,8 @@ def quant_rows(x: torch.Tensor, perm: Optional[torch.Tensor], sal: Optional[torc
     if not 0 <= Gi <= G:
         raise ValueError(f"int_groups={Gi} outside [0, {G}]")
     tail = (G - Gi) * g
+    if blocked and tail:
+        raise ValueError("a blocked input takes no hybrid split; call .dense() first")
     if tail and x2.dtype not in (torch.float16, torch.bfloat16):
         raise TypeError("the hybrid tail is stored in the 16-bit compute dtype; cast the input first")
     ld_codes = max(_round_up(Gi * g, 128), 128)
@@ -161,9 +174,15 @@ def quant_rows(x: torch.Tensor, perm: Optional[torch.Tensor], sal: Optional[torc
         ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
         ev[0].record(torch.cuda.current_stream(dev))
     with torch.cuda.device(dev):
-        check(lib.mq_quant_rows_split(x2.data_ptr(), R, K, _ld(x2), _dtype_code(x2), _ptr(smooth), _ptr(perm), Kn,
-                                      _ptr(sal), Ks, g, n_bits, Gi, codes.data_ptr(), ld_codes, scales.data_ptr(),
-                                      ld_scales, _ptr(sal_out), ld_sal, _stream(x)), "mq_quant_rows_split")
+        if blocked:
+            check(lib.mq_quant_rows_blocked(x2.data_ptr(), R, K, nb, S, R * S, S, _dtype_code(x2), _ptr(perm), Kn,
+                                            _ptr(sal), Ks, g, n_bits, codes.data_ptr(), ld_codes, scales.data_ptr(),
+                                            ld_scales, _ptr(sal_out), ld_sal, _stream(x)), "mq_quant_rows_blocked")
+        else:
+            check(lib.mq_quant_rows_split(x2.data_ptr(), R, K, _ld(x2), _dtype_code(x2), _ptr(smooth), _ptr(perm), Kn,
+                                          _ptr(sal), Ks, g, n_bits, Gi, codes.data_ptr(), ld_codes,
+                                          scales.data_ptr(), ld_scales, _ptr(sal_out), ld_sal, _stream(x)),
+                  "mq_quant_rows_split")
     if ev is not None:
         ev[1].record(torch.cuda.current_stream(dev))
         # algorithmic bytes: x read once, codes + fp32 scales + salient copy written once
@@ -241,11 +260,14 @@ def unpack_int4(packed: torch.Tensor, out: Optional[torch.Tensor] = None) -> tor
 # ---------------------------------------------------------------------------------------------- K2
 def mixed_gemm(a: Optional[QuantizedRows], w: Optional[QuantizedRows], bias: Optional[torch.Tensor],
                a_sal: Optional[torch.Tensor] = None, w_sal: Optional[torch.Tensor] = None,
-               Ks: Optional[int] = None, out_dtype: Optional[torch.dtype] = None) -> torch.Tensor:
+               Ks: Optional[int] = None, out_dtype: Optional[torch.dtype] = None,
+               out: Optional[torch.Tensor] = None) -> torch.Tensor:
     """y = sum_g a_scale*w_scale*(a_codes . w_codes) + a_sal . w_sal + bias   (replaces F.linear, fake_quant.py:306).
 
     ``a`` / ``w`` carry codes, scales and (optionally) the salient slices; pass ``a=None, w=None`` with explicit
-    ``a_sal`` / ``w_sal`` for the pure 16-bit GEMM of mode="reference"."""
+    ``a_sal`` / ``w_sal`` for the pure 16-bit GEMM of mode="reference".  ``out``: a [M, >= N rounded up to 8] tensor of
+    the compute dtype with unit column stride to write into (a column-parallel layer's own block of the gather
+    buffer)."""
     if a is not None:
         a_sal = a.sal if a_sal is None else a_sal
         w_sal = w.sal if w_sal is None else w_sal
@@ -272,7 +294,14 @@ def mixed_gemm(a: Optional[QuantizedRows], w: Optional[QuantizedRows], bias: Opt
         raise TypeError(f"mixed_gemm computes in float16 / bfloat16, got {dt}")
     if bias is not None:
         bias = bias.reshape(-1).to(device=dev, dtype=dt).contiguous()
-    y = torch.empty((M, _round_up(N, 8)), dtype=dt, device=dev)
+    if out is None:
+        y = torch.empty((M, _round_up(N, 8)), dtype=dt, device=dev)
+    else:
+        if out.dim() != 2 or out.shape[0] != M or out.shape[1] < _round_up(N, 8) or out.stride(1) != 1 \
+                or out.dtype != dt or out.device != dev or out.stride(0) % 8 or out.data_ptr() % 16:
+            raise ValueError(f"mixed_gemm: out must be a [{M}, >= {_round_up(N, 8)}] {dt} tensor with unit column "
+                             "stride and 16-byte aligned rows")
+        y = out
     ev = None
     if GEMM_EVENTS is not None:
         ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
@@ -300,7 +329,9 @@ def mixed_gemm(a: Optional[QuantizedRows], w: Optional[QuantizedRows], bias: Opt
 
 
 # ---------------------------------------------------------------------------------------------- K2d (decode, int4)
-DECODE_MAX_TOKENS = 64
+DECODE_MAX_TOKENS = 64      # what mq_decode_gemm accepts
+DECODE_PREFER_TOKENS = 32   # up to here it beats the prefill kernel on every measured shape (profiles/r02_decode_*);
+                            # at 33..64 tokens the 128-row tcgen05 tiles are already faster when the int8 codes are resident
 DECODE_EVENTS = None        # set to a list to collect (start_event, end_event, weight_bytes) per mq_decode_gemm
 
 
@@ -349,7 +380,8 @@ def pack_decode(w: QuantizedRows, dtype: Optional[torch.dtype] = None) -> Decode
     return DecodeWeights(nib=nib, sal=sal, rows=N, groups=G, group_size=g, Ks=Ks, dtype=dt)
 
 
-def decode_gemm(a: QuantizedRows, w: DecodeWeights, bias: Optional[torch.Tensor]) -> torch.Tensor:
+def decode_gemm(a: QuantizedRows, w: DecodeWeights, bias: Optional[torch.Tensor],
+                out: Optional[torch.Tensor] = None) -> torch.Tensor:
     """y for M <= 64 tokens from int4-resident weights (same contract as mixed_gemm; fake_quant.py:306)."""
     M, N, G, g = a.rows, w.rows, w.groups, w.group_size
     if M > DECODE_MAX_TOKENS:
@@ -362,7 +394,13 @@ def decode_gemm(a: QuantizedRows, w: DecodeWeights, bias: Optional[torch.Tensor]
         raise TypeError("salient slices of activation and weight must share a dtype")
     if bias is not None:
         bias = bias.reshape(-1).to(device=dev, dtype=dt).contiguous()
-    y = torch.empty((M, _round_up(N, 8)), dtype=dt, device=dev)
+    if out is None:
+        y = torch.empty((M, _round_up(N, 8)), dtype=dt, device=dev)
+    else:
+        if out.dim() != 2 or out.shape[0] != M or out.shape[1] < _round_up(N, 8) or out.stride(1) != 1 \
+                or out.dtype != dt or out.device != dev:
+            raise ValueError(f"decode_gemm: out must be a [{M}, >= {_round_up(N, 8)}] {dt} tensor, unit column stride")
+        y = out
     ev = None
     if DECODE_EVENTS is not None:
         ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))

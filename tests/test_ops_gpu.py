@@ -508,29 +508,32 @@ def test_decode_gemm_split_k_is_deterministic_and_exact(ops, mqlib, M, N, K, g, 
     assert float((y1.double() - ref).abs().max()) <= 1e-3 * float(ref.abs().max()) + 1e-3
 
 
-def test_decode_layer_releases_prefill_codes_and_rebuilds_them(ops):
+@pytest.mark.parametrize("g", [64, 128, 512])
+def test_decode_layer_releases_prefill_codes_and_rebuilds_them(ops, g):
     """W4A4Linear.prepare_decode(keep_prefill=False): the layer keeps 4 bits per non-salient weight on the device, runs
     M <= 64 through the decode kernel, and rebuilds the prefill operand bit for bit when a longer batch arrives."""
     from smoothquant_mixedprecision_b200 import fake_quant as fq
     torch.manual_seed(3)
-    K, N, g = 2048, 1536, 128
+    K, N = 2048, 1536
     lin = torch.nn.Linear(K, N).half().to(DEV)
     imp = torch.rand(K)
     mod = fq.W4A4Linear.from_float(lin, "per_group", "per_group", importance=imp, salient_prop=0.05, group_size=g,
-                                   mode="fused", sort_key=imp)
+                                   mode="fused", sort_key=imp, int_fraction=1.0)
     x16 = torch.randn(16, K, device=DEV).half()
     x300 = torch.randn(300, K, device=DEV).half()
     y16, y300, wd = mod(x16).clone(), mod(x300).clone(), mod.weight.clone()
     codes, wsal, full = mod.w_codes.clone(), mod.w_sal.clone(), mod.device_weight_bytes()
+    wsc = mod.w_scales.clone()
     mod.prepare_decode(keep_prefill=False)
-    assert mod.w_codes is None and mod.w_sal is None
-    assert mod.device_weight_bytes() < 0.62 * full
+    assert mod.w_codes is None and mod.w_sal is None and mod.w_scales is None    # scales live in the nibble stream
+    assert mod.device_weight_bytes() < 0.58 * full                  # 4-bit codes + 16-bit scales + the salient slice
     assert torch.equal(mod.weight, wd)                         # dequantised view from the nibble layout
     assert mod.w_codes is None                                 # ... without keeping the rebuilt operand
     yd = mod(x16)
     assert float((yd.float() - y16.float()).abs().max()) <= 2 * 2.0 ** -10 * float(y16.abs().max())
     assert torch.equal(mod(x300), y300)                        # > 64 tokens: prefill operand rebuilt, bit-identical
     assert torch.equal(mod.w_codes, codes) and torch.equal(mod.w_sal, wsal)
+    assert torch.equal(mod.w_scales[:, :N], wsc[:, :N])
     st = mod.packed_state()
     back = fq.W4A4Linear.from_packed(st, DEV)
     assert torch.equal(back(x300), y300)

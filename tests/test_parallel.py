@@ -64,6 +64,19 @@ def _worker(rank, world, port, N, M):
         assert got.shape == (M, N) and torch.equal(got, full), f"rank {rank}: gather mismatch"
         out = torch.empty(M, N, dtype=torch.float16)
         assert P.gather_columns(full[:, lo:hi].contiguous(), N, out=out) is out and torch.equal(out, full)
+        # blocked gather: same values, left in the collective's own [world, M, S] layout (sync, async, in-place block)
+        for async_op in (False, True):
+            bc = P.gather_columns_blocked(full[:, lo:hi].contiguous(), N, async_op=async_op)
+            S = P.shard_size(N, world)
+            assert tuple(bc.buf.shape) == (world, M, S) and tuple(bc.shape) == (M, N) and bc.dim() == 2
+            assert torch.equal(bc.dense(), full), f"rank {rank}: blocked gather mismatch"
+            for r in range(world):
+                a, b = P.shard_range(N, world, r)
+                assert torch.equal(bc.buf[r][:, : b - a], full[:, a:b])
+        buf = P.gather_buffer(M, N, world, torch.float16, "cpu")
+        buf[rank][:, : hi - lo].copy_(full[:, lo:hi])
+        bc = P.gather_columns_blocked(buf[rank][:, : hi - lo], N, buf=buf)
+        assert bc.buf is buf and torch.equal(bc.dense(), full)
         key = torch.full((5,), float(rank))
         key[rank] = 10.0
         red = P.allreduce_colmax(key.clone())
@@ -112,3 +125,76 @@ def test_column_shards_reproduce_unsharded_layer(world):
             assert sh.out_features == hi - lo and sh.full_out_features == N
             parts.append(sh(x, act_perm=perm) if mode == "reference" else sh(x))
         assert torch.equal(torch.cat(parts, dim=1), y), mode
+
+
+def test_blocked_columns_validates_its_buffer():
+    buf = torch.zeros(2, 3, 16)
+    assert tuple(P.BlockedColumns(buf, 20).shape) == (3, 20)
+    assert torch.equal(P.BlockedColumns(buf, 32).dense(), torch.zeros(3, 32))
+    with pytest.raises(ValueError):
+        P.BlockedColumns(buf, 16)                 # the second block would hold no column
+    with pytest.raises(ValueError):
+        P.BlockedColumns(buf, 33)
+    with pytest.raises(ValueError):
+        P.BlockedColumns(buf.permute(1, 0, 2), 20)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("world,K,g,p", [(2, 4096, 128, 0.05), (8, 11008, 128, 0.05), (4, 1000, 64, 0.1),
+                                         (2, 2048, 1024, 0.0), (8, 8192, 32, 0.05)])
+def test_row_quantiser_reads_the_gather_layout_in_place(world, K, g, p, dtype):
+    """mq_quant_rows_blocked on the [world, M, S] buffer an all-gather leaves behind == mq_quant_rows on the dense
+    tensor, bit for bit (codes, scales, salient copy), with and without a permutation."""
+    from smoothquant_mixedprecision_b200 import ops
+    torch.manual_seed(world * 1000 + K)
+    M = 333
+    S = P.shard_size(K, world)
+    x = (torch.randn(M, K, device="cuda") * torch.exp(0.5 * torch.randn(K, device="cuda"))).to(dtype)
+    buf = torch.full((world, M, S), 7.0, dtype=dtype, device="cuda")       # poison in the padding: must never be read
+    for r in range(world):
+        lo, hi = P.shard_range(K, world, r)
+        buf[r][:, : hi - lo] = x[:, lo:hi]
+    bc = P.BlockedColumns(buf, K)
+    assert torch.equal(bc.dense(), x)
+    ks = int(round(K * p))
+    order = torch.randperm(K, device="cuda")
+    sal = torch.sort(order[:ks]).values.int() if ks else None
+    for perm in (order[ks:].int(), None):
+        Kn = K - ks
+        if perm is None:                                       # contiguous mode: identity over the first Kn columns
+            sal_c = torch.arange(Kn, K, device="cuda").int() if ks else None
+            want = ops.quant_rows(x, None, sal_c, g, 4, Kn=Kn)
+            got = ops.quant_rows(bc, None, sal_c, g, 4, Kn=Kn)
+        else:
+            want = ops.quant_rows(x, perm, sal, g, 4)
+            got = ops.quant_rows(bc, perm, sal, g, 4)
+        assert torch.equal(got.codes[:, : want.groups * g], want.codes[:, : want.groups * g])
+        assert torch.equal(got.scales[:, :M], want.scales[:, :M])
+        if ks:
+            assert torch.equal(got.sal[:, :ks], want.sal[:, :ks])
+
+
+@pytest.mark.gpu
+def test_blocked_input_layer_matches_dense_input_layer():
+    """A W4A4Linear fed a BlockedColumns produces the same y as the same layer fed the dense tensor (bit for bit), for
+    prefill and decode row counts; a layer K1's blocked kernel does not cover falls back to .dense()."""
+    from smoothquant_mixedprecision_b200.fake_quant import W4A4Linear, clear_act_cache
+    torch.manual_seed(11)
+    K, N, g, world = 2048, 512, 128, 4
+    lin = torch.nn.Linear(K, N).half().cuda()
+    imp = torch.rand(K)
+    S = P.shard_size(K, world)
+    for M in (8, 700):
+        x = torch.randn(M, K, device="cuda").half()
+        buf = torch.zeros(world, M, S, dtype=torch.float16, device="cuda")
+        for r in range(world):
+            lo, hi = P.shard_range(K, world, r)
+            buf[r][:, : hi - lo] = x[:, lo:hi]
+        for frac in (1.0, 0.5):
+            mod = W4A4Linear.from_float(lin, "per_group", "per_group", importance=imp, salient_prop=0.05,
+                                        group_size=g, mode="fused", sort_key=imp, int_fraction=frac)
+            clear_act_cache()
+            y = mod(x).clone()
+            clear_act_cache()
+            assert torch.equal(mod(P.BlockedColumns(buf, K)), y), (M, frac)
