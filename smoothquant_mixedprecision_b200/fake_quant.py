@@ -152,9 +152,11 @@ def _int_groups(G, g, frac):
         frac = default_int_fraction(g)
     if not 0.0 <= frac <= 1.0:
         raise ValueError(f"int_fraction must be in [0, 1], got {frac}")
-    step = max(1, 128 // g)                 # the integer part must fill whole 128-column K blocks
-    gi = int(round(G * frac)) // step * step
-    return max(0, min(G, gi))
+    gi = int(round(G * frac))
+    if gi >= G:                             # everything on the integer engine: no tail, the last block is zero padded
+        return G
+    step = max(1, 128 // g)                 # a hybrid split must leave whole 128-column K blocks of integer groups
+    return max(0, gi // step * step)
 
 
 def _version_of(t):
