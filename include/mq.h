@@ -60,6 +60,19 @@ size_t mq_colstat_workspace_bytes(int64_t K, int kind);
 int mq_colstat(const void* x, int64_t M, int64_t K, int64_t ld, int dtype, int kind,
                float* out_key, void* workspace, size_t workspace_bytes, void* stream);
 
+/* mq_colstat for callers that may not allocate (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc): no workspace argument -- the per-split partial statistics go to a file-scope static __device__
+ * array of mq_colstat_static_max_bytes() = 4 MiB inside the library (held by every GPU that loads it, until exit).
+ * No counterpart in the reference.
+ *     Same result contract as mq_colstat (ABSMAX / ARGMAX identical; ABSMEAN / MEAN3STD may differ in the last
+ *     float bit when the split count had to be reduced to fit the scratch).
+ *     Limit: K * 24 bytes <= 4 MiB, i.e. K <= 174 762 columns; beyond that MQ_ERR_WORKSPACE with a message.
+ *     Calls no cudaMalloc / cudaFree / allocating routine.  All calls on a device SHARE the scratch: calls whose
+ *     kernels may overlap on the GPU (different streams) race -- serialise them.  The device must be current. */
+size_t mq_colstat_static_max_bytes(void);
+int mq_colstat_static(const void* x, int64_t M, int64_t K, int64_t ld, int dtype, int kind,
+                      float* out_key, void* stream);
+
 /* K0b stable ascending argsort of n float32 keys (ties -> ascending index; the canonical order of SURVEY F3).
  *     Replaces  torch.argsort(col_max_val)           fake_quant.py:116, :167
  *     With descending != 0: descending keys, ties still by ascending index  (fake_quant.py:268).

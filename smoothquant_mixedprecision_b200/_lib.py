@@ -25,6 +25,8 @@ SIGNATURES = {
     "mq_colstat_workspace_bytes": (_sz, [_i64, _i32]),
     "mq_colstat": (_i32, [_vp, _i64, _i64, _i64, _i32, _i32, _vp, _vp, _sz, _vp]),
     "mq_argsort_workspace_bytes": (_sz, [_i64]),
+    "mq_colstat_static_max_bytes": (_sz, []),
+    "mq_colstat_static": (_i32, [_vp, _i64, _i64, _i64, _i32, _i32, _vp, _vp]),
     "mq_argsort_stable": (_i32, [_vp, _vp, _i64, _i32, _vp, _vp, _sz, _vp]),
     "mq_quant_rows": (_i32, [_vp, _i64, _i64, _i64, _i32, _vp, _vp, _i64, _vp, _i64, _i32, _i32,
                              _vp, _i64, _vp, _i64, _vp, _i64, _vp]),

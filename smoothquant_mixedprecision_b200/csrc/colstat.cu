@@ -7,7 +7,15 @@
 //
 // HBM-bound: one coalesced pass over x (16-byte loads, a warp covers 512 contiguous bytes of a row), per-CTA
 // partial statistics in a workspace, then a fixed-order final reduction so that results are deterministic.
+#include <mutex>
+
 #include "common.cuh"
+
+// Scratch of mq_colstat_static (the no-allocation variant at the end of this file): per-split partial statistics.
+// Lives in every GPU context that loads the library until the process exits.  In HOST code this name is only a
+// stand-in for the symbol -- the device address comes from cudaGetSymbolAddress (static_scratch below).
+#define MQ_COLSTAT_STATIC_BYTES (4u << 20)
+static __device__ __align__(256) unsigned char g_colstat_static_scratch[MQ_COLSTAT_STATIC_BYTES];
 
 namespace {
 
@@ -177,6 +185,54 @@ int dispatch_kind(int kind, const void* x, int64_t M, int64_t K, int64_t ld, flo
   return MQ_ERR_ARG;
 }
 
+// ---------------------------------------------------------------- no-allocation variant (mq_colstat_static)
+// Same two kernels with the split count passed in (it is capped by what fits the static scratch).
+template <typename T, int KIND>
+int launch_colstat_static(const void* x, int64_t M, int64_t K, int64_t ld, float* out, Partial* ws, int splits,
+                          cudaStream_t st) {
+  constexpr int VEC = Vec<T>::N;
+  const bool vec_ok = (reinterpret_cast<uintptr_t>(x) % 16 == 0) && (ld % VEC == 0);
+  dim3 grid((unsigned)((K + 32 * VEC - 1) / (32 * VEC)), (unsigned)splits);
+  dim3 block(32, kRowLanes);
+  colstat_partial_kernel<T, KIND><<<grid, block, 0, st>>>(static_cast<const T*>(x), M, K, ld, ws, vec_ok);
+  MQ_CHECK_CUDA(cudaGetLastError());
+  colstat_final_kernel<KIND><<<(unsigned)((K + 255) / 256), 256, 0, st>>>(ws, splits, M, K, out);
+  MQ_CHECK_CUDA(cudaGetLastError());
+  return MQ_OK;
+}
+
+template <typename T>
+int dispatch_kind_static(int kind, const void* x, int64_t M, int64_t K, int64_t ld, float* out, Partial* ws, int splits,
+                         cudaStream_t st) {
+  switch (kind) {
+    case MQ_STAT_ABSMAX: return launch_colstat_static<T, MQ_STAT_ABSMAX>(x, M, K, ld, out, ws, splits, st);
+    case MQ_STAT_ABSMEAN: return launch_colstat_static<T, MQ_STAT_ABSMEAN>(x, M, K, ld, out, ws, splits, st);
+    case MQ_STAT_MEAN3STD: return launch_colstat_static<T, MQ_STAT_MEAN3STD>(x, M, K, ld, out, ws, splits, st);
+    case MQ_STAT_ARGMAX: return launch_colstat_static<T, MQ_STAT_ARGMAX>(x, M, K, ld, out, ws, splits, st);
+  }
+  mq_set_error("mq_colstat_static: unknown kind %d", kind);
+  return MQ_ERR_ARG;
+}
+
+// Device address of g_colstat_static_scratch on the CURRENT device, resolved once per device (set-up) and kept.
+constexpr int kMaxDevices = 64;
+int static_scratch(Partial** out) {
+  static std::mutex mu;
+  static void* ptrs[kMaxDevices] = {};
+  int dev = -1;
+  MQ_CHECK_CUDA(cudaGetDevice(&dev));
+  MQ_CHECK_ARG(dev >= 0 && dev < kMaxDevices, "mq_colstat_static: device ordinal %d outside [0, %d)", dev, kMaxDevices);
+  std::lock_guard<std::mutex> lock(mu);
+  if (ptrs[dev] == nullptr) {
+    void* p = nullptr;
+    MQ_CHECK_CUDA(cudaGetSymbolAddress(&p, g_colstat_static_scratch));
+    MQ_CHECK_ARG(p != nullptr, "mq_colstat_static: cudaGetSymbolAddress returned a null address");
+    ptrs[dev] = p;
+  }
+  *out = static_cast<Partial*>(ptrs[dev]);
+  return MQ_OK;
+}
+
 // ---------------------------------------------------------------- K0b: stable argsort by ranking
 // rank_i = #{ j : key_j < key_i  or (key_j == key_i and j < i) }  -> out[rank_i] = id_i.  O(n^2) compares, fully
 // parallel and stable by construction; n <= 65535 keys (28 672 for Llama-2-70B) is ~1e9 compares at most.
@@ -253,6 +309,38 @@ int mq_colstat(const void* x, int64_t M, int64_t K, int64_t ld, int dtype, int k
     case MQ_F32: return dispatch_kind<float>(kind, x, M, K, ld, out_key, workspace, st);
   }
   mq_set_error("mq_colstat: unknown dtype %d", dtype);
+  return MQ_ERR_ARG;
+}
+
+size_t mq_colstat_static_max_bytes(void) { return (size_t)MQ_COLSTAT_STATIC_BYTES; }
+
+int mq_colstat_static(const void* x, int64_t M, int64_t K, int64_t ld, int dtype, int kind, float* out_key,
+                      void* stream) {
+  MQ_CHECK_ARG(x && out_key, "mq_colstat_static: null pointer");
+  MQ_CHECK_ARG(M >= 1 && K >= 1 && ld >= K, "mq_colstat_static: bad shape M=%lld K=%lld ld=%lld", (long long)M,
+               (long long)K, (long long)ld);
+  MQ_CHECK_ARG(M < (1ll << 31), "mq_colstat_static: M too large");
+  const size_t per_split = (size_t)K * sizeof(Partial);
+  if (per_split > (size_t)MQ_COLSTAT_STATIC_BYTES) {
+    mq_set_error("mq_colstat_static: K=%lld needs %zu bytes of scratch, the static scratch holds %zu (at most %zu "
+                 "columns); use mq_colstat with a caller-provided workspace", (long long)K, per_split,
+                 (size_t)MQ_COLSTAT_STATIC_BYTES, (size_t)MQ_COLSTAT_STATIC_BYTES / sizeof(Partial));
+    return MQ_ERR_WORKSPACE;
+  }
+  int splits = colstat_splits(M);
+  const int fit = (int)((size_t)MQ_COLSTAT_STATIC_BYTES / per_split);
+  if (splits > fit) splits = fit;
+  Partial* ws = nullptr;
+  int rc = static_scratch(&ws);
+  if (rc) return rc;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  // nothing has to start at zero: the partial kernel writes every (split, column < K) cell the final kernel reads
+  switch (dtype) {
+    case MQ_F16: return dispatch_kind_static<__half>(kind, x, M, K, ld, out_key, ws, splits, st);
+    case MQ_BF16: return dispatch_kind_static<__nv_bfloat16>(kind, x, M, K, ld, out_key, ws, splits, st);
+    case MQ_F32: return dispatch_kind_static<float>(kind, x, M, K, ld, out_key, ws, splits, st);
+  }
+  mq_set_error("mq_colstat_static: unknown dtype %d", dtype);
   return MQ_ERR_ARG;
 }
 
