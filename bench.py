@@ -67,6 +67,9 @@ def parse():
     ap.add_argument("--tp-chunks", type=int, default=2,
                     help="tp: row chunks of the batch pipelined through the layers so that one chunk's all-gather "
                          "overlaps the other chunk's GEMM")
+    ap.add_argument("--transport", default="peer", choices=["peer", "nccl"],
+                    help="tp: how gathered outputs travel -- peer = copy engines over peer-mapped memory, ordered by "
+                         "stream memory operations (parallel.PeerGather, no SMs); nccl = all_gather_into_tensor")
     ap.add_argument("--no-decode", action="store_true")
     return ap.parse_args()
 
@@ -473,13 +476,27 @@ def gpu_arm(args):
                                "quantiser_ms": float(t[2])},
                 "overlapped": {"ms_per_step": ms, "exposed_comm_ms": max(0.0, ms - (ms_serial - float(t[0])))},
                 "limiting_collective": {
-                    "what": "all_gather_into_tensor of one row chunk of a gathered layer output "
+                    "what": "all-gather of one row chunk of a gathered layer output "
                             f"([{world}, {rows[0][1] - rows[0][0]}, S] fp16, in place)",
                     "bytes_received_per_rank": worst[0], "calls_per_step": worst[1][1] // args.steps,
                     "ms_per_call": per_call_ms, "algbw_GBs": worst[0] / per_call_ms / 1e6,
                     "busbw_note": "bytes received per rank / time: (p-1)/p of the gathered tensor over NVLink"}}
         return r
 
+    transport = None
+    if tp:
+        from smoothquant_mixedprecision_b200 import parallel as par
+        transport = "nccl"
+        if args.transport == "peer":
+            try:
+                par.enable_peer_gather()
+                transport = "peer"
+            except Exception as e:      # no peer-mapped memory on this box: NCCL carries the gathers
+                print(f"bench.py: peer transport unavailable ({type(e).__name__}: {e}); using NCCL", file=sys.stderr)
+        ok = torch.tensor([1 if transport == "peer" else 0], device=dev)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        if int(ok.item()) == 0:
+            par.TRANSPORT, transport = "nccl", "nccl"
     stack, x0 = build_stack(args.layers, M, dev, seed=1234 + (0 if tp else rank), tp=(rank, world) if tp else None)
     job_tokens = M if tp else world * M
     main = measure(stack, x0, tp, True)
@@ -536,7 +553,7 @@ def gpu_arm(args):
                                    "prefill 16x2048 tokens per GPU (dp) or per job (tp)", "tokens_per_gpu": M, "layers": args.layers,
                        "group_size": GROUP, "salient_prop": SALIENT,
                        "parallelism": (f"tp{world}: column-parallel over out_features, ONE {M}-token batch per job; "
-                                       "v/o/up/down outputs all-gathered in place into [p, M, S] (NCCL, async, "
+                                       "v/o/up/down outputs all-gathered in place into [p, M, S] (" + str(transport) + ", async, "
                                        f"{max(1, args.tp_chunks)} row chunks) and quantised from that layout") if tp
                        else f"dp{world}",
                        "l2": "inputs (268 MB activations, 6.9 GB weights) exceed the 126 MB L2; no flush"},
@@ -562,6 +579,10 @@ def gpu_arm(args):
             "clocks": clocks}
     if tp:
         line["column_parallel"] = main["comm"]
+        line["column_parallel"]["transport"] = (
+            "peer-mapped memory: copy-engine pulls over NVLink ordered by stream memory operations (mq_peer_gather, "
+            "no SMs); process group (NCCL) used for set-up and the timing barriers only" if transport == "peer"
+            else "NCCL all_gather_into_tensor, in place")
     if other is not None:
         line["data_parallel"] = {
             "value": world * M / (other["ms"] * 1e-3), "unit": "tokens/s", "scaling": "weak",

@@ -214,6 +214,25 @@ int mq_gemm_fault(unsigned int* out8_host);
  * min(n_ctas, 256) records to out_host (HOST pointer).  Synchronises the device. */
 int mq_gemm_profile(unsigned long long* out_host, int n_ctas);
 
+/* ------------------------------------------------------------------------------------------------------------
+ * Column-parallel plumbing; the reference is single-GPU (its only multi-GPU touchpoint is
+ * device_map="auto", ppl_eval.py:70), so these have no counterpart there.
+ *
+ * mq_peer_gather: all-gather of the [M, S] column blocks of a column-parallel layer over peer-mapped memory
+ * (cuMem mappings with peer access, e.g. torch.distributed._symmetric_memory), done by the copy engines and
+ * ordered by stream memory operations -- no kernel, so it runs underneath the persistent GEMM of the next chunk.
+ *     bufs[world]   device address, in THIS process, of every rank's gather buffer [world][M][S]; the caller's GEMM
+ *                   has written block `rank` of bufs[rank] in stream order before the call
+ *     flags[world]  device address of every rank's flag block, uint32 [2][world] (ready, pulled), zero at start
+ *     seq           1, 2, 3, ... : the same sequence of calls on every rank
+ *     On return the stream holds: publish ready, and per peer wait-ready / DMA its block into bufs[rank] / publish
+ *     pulled.  Work queued on `stream` afterwards sees the full [world][M][S].
+ * mq_peer_wait_pulled: makes `stream` wait until every peer has copied this rank's block of gather `seq` out --
+ *     call it before overwriting a gather buffer last used by gather `seq`. */
+int mq_peer_gather(const uint64_t* bufs, const uint64_t* flags, int rank, int world, size_t block_bytes,
+                   uint32_t seq, void* stream);
+int mq_peer_wait_pulled(const uint64_t* flags, int rank, int world, uint32_t seq, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

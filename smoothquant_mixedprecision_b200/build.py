@@ -17,7 +17,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 BUILD = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "libmq.so")
-SOURCES = ["common.cu", "tma_host.cu", "colstat.cu", "quant_rows.cu", "mixed_gemm.cu", "decode_gemm.cu"]
+SOURCES = ["common.cu", "tma_host.cu", "colstat.cu", "quant_rows.cu", "mixed_gemm.cu", "decode_gemm.cu", "peer_gather.cu"]
 HEADERS = sorted(os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith(".cuh")) + \
     [os.path.join(os.path.dirname(HERE), "include", "mq.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",

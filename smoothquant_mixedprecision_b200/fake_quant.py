@@ -458,6 +458,11 @@ class W4A4Linear(nn.Module):
         xin = x2 if x2.dtype == cdt else x2.to(cdt)
         if blocked_out:
             # the GEMM writes this rank's block of the gather buffer; the collective then runs in place and async
+            peer = parallel.peer_gather_for(self.tp_group)
+            if peer is not None:                # copy engines over peer-mapped memory (parallel.PeerGather)
+                slot = peer.buffer(x2.shape[0], self.full_out_features, cdt)
+                self._fused_gemm(x, xin, cdt, out=slot["buf"][self.tp_rank])
+                return peer.gather(slot, self.full_out_features, parallel.ASYNC_GATHER)
             buf = parallel.gather_buffer(x2.shape[0], self.full_out_features, self.tp_world, cdt, x2.device)
             y = self._fused_gemm(x, xin, cdt, out=buf[self.tp_rank])
             return parallel.gather_columns_blocked(buf[self.tp_rank][:, : y.shape[1]], self.full_out_features,

@@ -189,6 +189,123 @@ def gather_columns_blocked(y_local: torch.Tensor, n_out: int, group=None, buf: O
     return BlockedColumns(buf, n_out, work if async_op else None)
 
 
+class PeerGather:
+    """SM-free replacement for the NCCL all-gather of gather_columns_blocked on one NVLink box.
+
+    Gather buffers [world, M, S] and a flag block live in peer-mapped memory (torch.distributed._symmetric_memory =
+    cuMem allocations mapped into every rank of the group); the transfer is mq_peer_gather (include/mq.h): copy-engine
+    pulls over NVLink ordered by stream memory operations, issued on a side stream, so it runs underneath the GEMMs
+    of the next row chunk instead of queueing behind them for SMs.
+
+    Buffers come from a ring of ``ring`` buffers per (M, S, dtype): the BlockedColumns a layer returns is valid until
+    ``ring`` more gathers of the same shape have been issued (``dense()`` copies).  Every rank must issue the same
+    sequence of gathers."""
+
+    def __init__(self, group=None, ring: int = 4):
+        import ctypes as C
+        import torch.distributed._symmetric_memory as symm
+        from . import _lib
+        self._C, self._symm, self._lib = C, symm, _lib
+        self.group = group if group is not None else dist.group.WORLD
+        self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        self.ring = max(2, int(ring))
+        self.dev = torch.device("cuda", torch.cuda.current_device())
+        self.seq = 0
+        self.rings = {}                       # (M, S, dtype) -> {"slots": [...], "next": i}
+        self.stream = torch.cuda.Stream(device=self.dev, priority=-1)
+        self.flags = symm.empty(max(64, 2 * self.world), dtype=torch.int32, device=self.dev)
+        self.flags.zero_()
+        self._fh = symm.rendezvous(self.flags, self.group)
+        self._flag_ptrs = (C.c_uint64 * self.world)(*[int(p) for p in self._fh.buffer_ptrs])
+        torch.cuda.synchronize(self.dev)
+        self._fh.barrier()                    # nobody publishes a flag before everyone has zeroed theirs
+        torch.cuda.synchronize(self.dev)
+
+    def _slot(self, M, S, dtype):
+        key = (M, S, dtype)
+        ring = self.rings.get(key)
+        if ring is None:
+            ring = self.rings[key] = {"slots": [], "next": 0}
+        if len(ring["slots"]) < self.ring:    # collective: every rank allocates the same buffers in the same order
+            buf = self._symm.empty((self.world, M, S), dtype=dtype, device=self.dev)
+            h = self._symm.rendezvous(buf, self.group)
+            ptrs = (self._C.c_uint64 * self.world)(*[int(p) for p in h.buffer_ptrs])
+            slot = {"buf": buf, "h": h, "ptrs": ptrs, "last": 0}
+            ring["slots"].append(slot)
+            return slot
+        slot = ring["slots"][ring["next"]]
+        ring["next"] = (ring["next"] + 1) % self.ring
+        return slot
+
+    def buffer(self, M: int, n_out: int, dtype) -> dict:
+        """Next gather buffer of the ring for this shape; the current stream is made to wait until every peer has
+        copied this rank's block of the buffer's previous gather out, so the GEMM may overwrite it."""
+        slot = self._slot(M, shard_size(n_out, self.world), dtype)
+        if slot["last"]:
+            st = torch.cuda.current_stream(self.dev).cuda_stream
+            self._lib.check(self._lib.lib.mq_peer_wait_pulled(self._flag_ptrs, self.rank, self.world, slot["last"], st),
+                            "mq_peer_wait_pulled")
+        return slot
+
+    def gather(self, slot: dict, n_out: int, async_op: bool = True) -> "BlockedColumns":
+        """All-gather `slot` (this rank's block already written on the current stream)."""
+        buf = slot["buf"]
+        cur = torch.cuda.current_stream(self.dev)
+        self.seq += 1
+        slot["last"] = self.seq
+        block = buf.shape[1] * buf.shape[2] * buf.element_size()
+        ev = None
+        if async_op:
+            self.stream.wait_stream(cur)
+            st = self.stream
+        else:
+            st = cur
+            if COMM_EVENTS is not None:
+                ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+                ev[0].record(cur)
+        self._lib.check(self._lib.lib.mq_peer_gather(slot["ptrs"], self._flag_ptrs, self.rank, self.world, block,
+                                                     self.seq, st.cuda_stream), "mq_peer_gather")
+        if ev is not None:
+            ev[1].record(cur)
+            COMM_EVENTS.append((ev[0], ev[1], (self.world - 1) * block))
+        if not async_op:
+            return BlockedColumns(buf, n_out)
+        done = torch.cuda.Event()
+        done.record(self.stream)
+        return BlockedColumns(buf, n_out, _EventWork(done, self.dev))
+
+
+class _EventWork:
+    """wait() = the current stream waits for an event (the interface BlockedColumns expects of a collective's Work)."""
+
+    def __init__(self, event, dev):
+        self.event, self.dev = event, dev
+
+    def wait(self):
+        torch.cuda.current_stream(self.dev).wait_event(self.event)
+
+
+_PEER = {}              # id(group) -> PeerGather
+TRANSPORT = "nccl"      # "peer": gathers of blocked-output layers go through PeerGather (set by enable_peer_gather)
+
+
+def enable_peer_gather(group=None, ring: int = 4) -> PeerGather:
+    """Collective: set up the peer-memory transport for `group` (one NVLink box) and make blocked-output layers use
+    it.  Raises if symmetric memory cannot be established; the NCCL path stays available (TRANSPORT = "nccl")."""
+    global TRANSPORT
+    key = id(group) if group is not None else 0
+    if key not in _PEER:
+        _PEER[key] = PeerGather(group, ring)
+    TRANSPORT = "peer"
+    return _PEER[key]
+
+
+def peer_gather_for(group=None) -> Optional[PeerGather]:
+    if TRANSPORT != "peer":
+        return None
+    return _PEER.get(id(group) if group is not None else 0)
+
+
 def allreduce_colmax(key: torch.Tensor, group=None) -> torch.Tensor:
     """max over data-parallel ranks of a per-column statistic: what the literal dynamic sort (fake_quant.py:113, a
     reduction over ALL tokens of the batch) needs when the tokens of one batch are spread over ranks."""

@@ -198,3 +198,56 @@ def test_blocked_input_layer_matches_dense_input_layer():
             y = mod(x).clone()
             clear_act_cache()
             assert torch.equal(mod(P.BlockedColumns(buf, K)), y), (M, frac)
+
+
+def _nccl_pipeline_worker(rank, world, port):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    try:
+        import bench
+        bench.HIDDEN, bench.INTER = 1024, 2752
+        H, I = bench.HIDDEN, bench.INTER
+        bench.SHAPES = {"q_proj": (H, H), "k_proj": (H, H), "v_proj": (H, H), "o_proj": (H, H), "gate_proj": (I, H),
+                        "up_proj": (I, H), "down_proj": (H, I)}
+        M = 640
+        full, x0 = bench.build_stack(2, M, dev, seed=5)
+        want = bench.run_stack(full, x0).clone()
+        tpst, x1 = bench.build_stack(2, M, dev, seed=5, tp=(rank, world))
+        assert torch.equal(x0, x1)
+        for transport, asynchronous in (("nccl", True), ("nccl", False), ("peer", True), ("peer", False)):
+            if transport == "peer":
+                P.enable_peer_gather(ring=3)
+            P.ASYNC_GATHER = asynchronous
+            for chunks in (1, 2, 3, 2, 1):      # the repeats re-use ring buffers (overwrite-after-pulled ordering)
+                rows = [(i * M // chunks, (i + 1) * M // chunks) for i in range(chunks)]
+                outs = bench.run_stack_tp(tpst, [x0[a:b] for a, b in rows])
+                assert all(isinstance(o, P.BlockedColumns) for o in outs)
+                got = torch.cat([o.dense() for o in outs])
+                assert torch.equal(got, want), (rank, transport, asynchronous, chunks,
+                                                float((got - want).abs().max()))
+        # decode row counts take the decode kernel on every shard
+        for mods in tpst:
+            for m in mods.values():
+                m.prepare_decode()
+        for mods in full:
+            for m in mods.values():
+                m.prepare_decode()
+        xd = x0[:16].contiguous()
+        want_d = bench.run_stack(full, xd)
+        got_d = bench.run_stack_tp(tpst, [xd])[0].dense()
+        assert torch.equal(got_d, want_d), (rank, "decode")
+        torch.cuda.synchronize()
+    finally:
+        P.ASYNC_GATHER, P.TRANSPORT = True, "nccl"
+        dist.destroy_process_group()
+
+
+@pytest.mark.gpu
+def test_nccl_world2_column_parallel_pipeline_is_bit_identical():
+    """Two GPUs, NCCL: the column-parallel pass over row chunks (in-place async all-gathers into [p, M, S], K1 reading
+    that layout) reproduces the single-GPU stack bit for bit.  Skipped on a one-GPU box."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    mp.spawn(_nccl_pipeline_worker, args=(2, _free_port()), nprocs=2, join=True)
