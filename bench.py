@@ -67,9 +67,11 @@ def parse():
     ap.add_argument("--tp-chunks", type=int, default=2,
                     help="tp: row chunks of the batch pipelined through the layers so that one chunk's all-gather "
                          "overlaps the other chunk's GEMM")
-    ap.add_argument("--transport", default="peer", choices=["peer", "nccl"],
+    ap.add_argument("--transport", default="auto", choices=["auto", "peer", "nccl"],
                     help="tp: how gathered outputs travel -- peer = copy engines over peer-mapped memory, ordered by "
-                         "stream memory operations (parallel.PeerGather, no SMs); nccl = all_gather_into_tensor")
+                         "stream memory operations (parallel.PeerGather, no SMs); nccl = all_gather_into_tensor; "
+                         "auto = peer up to 4 GPUs, nccl beyond (measured: profiles/r02_tp_sweep.txt)")
+    ap.add_argument("--peer-lanes", type=int, default=None, help="peer transport: copy streams pulling in parallel")
     ap.add_argument("--no-decode", action="store_true")
     return ap.parse_args()
 
@@ -487,9 +489,9 @@ def gpu_arm(args):
     if tp:
         from smoothquant_mixedprecision_b200 import parallel as par
         transport = "nccl"
-        if args.transport == "peer":
+        if args.transport == "peer" or (args.transport == "auto" and world <= 4):
             try:
-                par.enable_peer_gather()
+                par.enable_peer_gather(lanes=args.peer_lanes)
                 transport = "peer"
             except Exception as e:      # no peer-mapped memory on this box: NCCL carries the gathers
                 print(f"bench.py: peer transport unavailable ({type(e).__name__}: {e}); using NCCL", file=sys.stderr)

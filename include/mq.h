@@ -225,12 +225,14 @@ int mq_gemm_profile(unsigned long long* out_host, int n_ctas);
  *                   has written block `rank` of bufs[rank] in stream order before the call
  *     flags[world]  device address of every rank's flag block, uint32 [2][world] (ready, pulled), zero at start
  *     seq           1, 2, 3, ... : the same sequence of calls on every rank
- *     On return the stream holds: publish ready, and per peer wait-ready / DMA its block into bufs[rank] / publish
- *     pulled.  Work queued on `stream` afterwards sees the full [world][M][S].
+ *     streams[n]    cudaStream_t handles (as integers): the peers are dealt round-robin over them so that several
+ *                   copy engines pull in parallel; every one must already be ordered after the caller's GEMM
+ *     On return the streams hold: publish ready (streams[0]), and per peer wait-ready / DMA its block into
+ *     bufs[rank] / publish pulled.  Work ordered after ALL the streams sees the full [world][M][S].
  * mq_peer_wait_pulled: makes `stream` wait until every peer has copied this rank's block of gather `seq` out --
  *     call it before overwriting a gather buffer last used by gather `seq`. */
 int mq_peer_gather(const uint64_t* bufs, const uint64_t* flags, int rank, int world, size_t block_bytes,
-                   uint32_t seq, void* stream);
+                   uint32_t seq, const uint64_t* streams, int n_streams);
 int mq_peer_wait_pulled(const uint64_t* flags, int rank, int world, uint32_t seq, void* stream);
 
 #ifdef __cplusplus

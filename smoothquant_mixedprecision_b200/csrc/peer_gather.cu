@@ -67,22 +67,24 @@ int check_common(const char* fn, const uint64_t* flags, int rank, int world) {
 extern "C" {
 
 int mq_peer_gather(const uint64_t* bufs, const uint64_t* flags, int rank, int world, size_t block_bytes, uint32_t seq,
-                   void* stream) {
+                   const uint64_t* streams, int n_streams) {
   int rc = check_common("mq_peer_gather", flags, rank, world);
   if (rc) return rc;
   MQ_CHECK_ARG(bufs && block_bytes > 0 && block_bytes % 16 == 0, "mq_peer_gather: bad buffer table / block size");
-  CUstream st = static_cast<CUstream>(stream);
+  MQ_CHECK_ARG(streams && n_streams >= 1 && n_streams <= 16, "mq_peer_gather: 1..16 streams, got %d", n_streams);
   const uint64_t w4 = (uint64_t)world * 4;
+  CUstream st0 = reinterpret_cast<CUstream>(streams[0]);
   for (int s = 1; s < world; ++s) {                       // ready[rank] of every peer
     const int p = (rank + s) % world;
-    MQ_CHECK_DRV(write32()(st, (CUdeviceptr)(flags[p] + 4ull * rank), seq, CU_STREAM_WRITE_VALUE_DEFAULT));
+    MQ_CHECK_DRV(write32()(st0, (CUdeviceptr)(flags[p] + 4ull * rank), seq, CU_STREAM_WRITE_VALUE_DEFAULT));
   }
   for (int s = 1; s < world; ++s) {                       // staggered: rank r starts with its left neighbour
     const int p = (rank + world - s) % world;
+    CUstream st = reinterpret_cast<CUstream>(streams[(s - 1) % n_streams]);   // lanes = copy engines in parallel
     MQ_CHECK_DRV(wait32()(st, (CUdeviceptr)(flags[rank] + 4ull * p), seq, CU_STREAM_WAIT_VALUE_GEQ));
     const uint64_t off = (uint64_t)p * block_bytes;
     MQ_CHECK_CUDA(cudaMemcpyAsync(reinterpret_cast<void*>(bufs[rank] + off), reinterpret_cast<const void*>(bufs[p] + off),
-                                  block_bytes, cudaMemcpyDeviceToDevice, static_cast<cudaStream_t>(stream)));
+                                  block_bytes, cudaMemcpyDeviceToDevice, reinterpret_cast<cudaStream_t>(st)));
     MQ_CHECK_DRV(write32()(st, (CUdeviceptr)(flags[p] + w4 + 4ull * rank), seq, CU_STREAM_WRITE_VALUE_DEFAULT));
   }
   return MQ_OK;
