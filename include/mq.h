@@ -132,6 +132,22 @@ int mq_quant_rows_blocked(const void* x, int64_t R, int64_t K, int x_blocks, int
                           int8_t* out_codes, int64_t ld_codes, float* out_scales, int64_t ld_scales,
                           void* out_sal, int64_t ld_sal, void* stream);
 
+/* Producer-side fusion: the norm in front of q/k/v and gate/up fused into the row quantiser -- x is
+ * read once, the normalised row lives only in shared memory.
+ *     Replaces  LlamaRMSNorm / nn.LayerNorm (whose weights smooth_lm has already divided by the smoothing scale,
+ *               smooth.py:126-141, :12-29, :33-54) followed by mq_quant_rows on its output:
+ *       MQ_NORM_RMS    y = rn(w * rn(x32 * rsqrt(mean(x32^2) + eps)))        (16-bit roundings as in transformers)
+ *       MQ_NORM_LAYER  y = rn(((x32 - mean) * rsqrt(var + eps)) * w32 + b32)  (torch.nn.functional.layer_norm)
+ *     then codes / scales / salient copy of y exactly as mq_quant_rows (bit-identical given the same y).
+ *     out_y (nullable): the normalised rows [R, ld_y], for consumers outside the path and for the parity tests.
+ *     16-bit dtypes, K % 8 == 0, K <= 16384, power-of-two group sizes 32..1024; otherwise MQ_ERR_UNSUPPORTED. */
+enum mq_norm_kind { MQ_NORM_RMS = 1, MQ_NORM_LAYER = 2 };
+int mq_norm_quant_rows(const void* x, int64_t R, int64_t K, int64_t ld, int dtype, int norm_kind,
+                       const void* norm_weight, const void* norm_bias, float eps,
+                       const int32_t* perm, int64_t Kn, const int32_t* sal, int64_t Ks, int group_size, int n_bits,
+                       int8_t* out_codes, int64_t ld_codes, float* out_scales, int64_t ld_scales,
+                       void* out_sal, int64_t ld_sal, void* out_y, int64_t ld_y, void* stream);
+
 /* Same arithmetic, reference-shaped output: out [R, K] (dtype) holds code*scale at the ORIGINAL column of every
  * permuted position and x itself at every column not listed in perm (salient pass-through).
  *     Replaces  quantize_activation_per_group_absmax_sort   fake_quant.py:105-154  (perm = argsort of the key)

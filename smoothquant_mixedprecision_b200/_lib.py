@@ -34,6 +34,8 @@ SIGNATURES = {
                                    _vp, _i64, _vp, _i64, _vp, _i64, _vp]),
     "mq_quant_rows_blocked": (_i32, [_vp, _i64, _i64, _i32, _i64, _i64, _i64, _i32, _vp, _i64, _vp, _i64, _i32, _i32,
                                      _vp, _i64, _vp, _i64, _vp, _i64, _vp]),
+    "mq_norm_quant_rows": (_i32, [_vp, _i64, _i64, _i64, _i32, _i32, _vp, _vp, C.c_float, _vp, _i64, _vp, _i64, _i32,
+                                  _i32, _vp, _i64, _vp, _i64, _vp, _i64, _vp, _i64, _vp]),
     "mq_fakequant_rows": (_i32, [_vp, _i64, _i64, _i64, _i32, _vp, _i64, _i32, _i32, _vp, _i64, _vp]),
     "mq_fakequant_tensor": (_i32, [_vp, _i64, _i32, _i32, _vp, _vp, _sz, _vp]),
     "mq_pack_int4": (_i32, [_vp, _i64, _i64, _i64, _vp, _i64, _vp]),

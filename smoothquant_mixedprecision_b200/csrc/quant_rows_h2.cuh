@@ -88,6 +88,15 @@ struct H2Args {
   int x_blocks;        // column blocks of the input (1 = plain row-major)
   int64_t blk_cols, blk_stride;
   float rq;            // rn(1 / qmax)
+  // fused producer norm (mq_norm_quant_rows): 0 none, 1 RMSNorm, 2 LayerNorm; the staged rows are normalised in place
+  // before they are quantised
+  int norm;
+  int norm_parts;      // consumer warps sharing one row in the norm phase (power of two)
+  const void* norm_w;  // [K] T
+  const void* norm_b;  // [K] T or NULL (LayerNorm)
+  float eps;
+  void* out_y;         // optional dump of the normalised rows [R, ld_y] T (tests; consumers outside the path)
+  int64_t ld_y;
 };
 
 // reciprocal-mantissa table: entry m = bits to ADD to the exponent part of y = rn_T(1 / 1.m) (carry into the exponent
@@ -140,7 +149,98 @@ __device__ __forceinline__ GroupK<T> group_consts(uint32_t amax16, float qmax, f
   return k;
 }
 
-template <typename T, bool GATHER>
+__device__ __forceinline__ void sts_u128(uint32_t addr, const uint4& v) {
+  asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" :: "r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+__device__ __forceinline__ void cons_bar_sync() {      // the 16 consumer warps only (the producer warp never joins)
+  asm volatile("bar.sync 1, %0;" :: "n"(kConsThreads) : "memory");
+}
+constexpr int kNormMaxRows = 64;                        // rows per stage the norm phase supports (partial-sum slots)
+
+// Normalise the `nr` staged rows of one stage in place.  Work unit = (row, part): `parts` consumer warps share a row.
+//   RMSNorm  (transformers LlamaRMSNorm.forward): y = rn_T(w * rn_T(x32 * rsqrt(mean(x32^2) + eps)))
+//   LayerNorm (torch.nn.functional.layer_norm on a 16-bit tensor): y = rn_T(((x32 - mean) * rstd) * w32 + b32)
+// Statistics are fp32 sums over all K columns of the row (salient ones included: the norm knows no partition).
+template <typename T, int NORM>
+__device__ __forceinline__ void norm_stage(const H2Args& a, uint32_t sbase, uint32_t pitch_b, int nr, int64_t r0, int K,
+                                           uint32_t w_sm, uint32_t b_sm, float2* psum, int warp, int lane) {
+  using V2 = typename Pk<T>::V2;
+  const int P = a.norm_parts, part = warp & (P - 1), wrow = warp / P, rows_per_round = kConsWarps / P;
+  const int nvec = K >> 3, vpp = (nvec + P - 1) / P;
+  const int v0 = part * vpp, v1 = min(nvec, v0 + vpp);
+  for (int rb = 0; rb < a.rps; rb += rows_per_round) {
+    const int r = rb + wrow;
+    const bool have = r < nr;
+    const uint32_t row_a = sbase + (uint32_t)min(r, a.rps - 1) * pitch_b;
+    float s1 = 0.f, s2 = 0.f;
+    if (have) {
+      for (int v = v0 + lane; v < v1; v += 32) {
+        const uint4 d = lds_u128(row_a + (uint32_t)v * 16u);
+        const uint32_t wd[4] = {d.x, d.y, d.z, d.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const float f0 = Pk<T>::to_f(wd[j] & 0xFFFFu), f1 = Pk<T>::to_f(wd[j] >> 16);
+          s2 = fmaf(f0, f0, s2);
+          s2 = fmaf(f1, f1, s2);
+          if (NORM == 2) s1 += f0 + f1;
+        }
+      }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      s2 += __shfl_xor_sync(0xffffffffu, s2, o);
+      if (NORM == 2) s1 += __shfl_xor_sync(0xffffffffu, s1, o);
+    }
+    if (lane == 0 && r < a.rps) psum[r * P + part] = make_float2(s1, s2);
+    cons_bar_sync();
+    if (have) {
+      float t1 = 0.f, t2 = 0.f;
+      for (int pp = 0; pp < P; ++pp) {
+        const float2 v = psum[r * P + pp];
+        t1 += v.x;
+        t2 += v.y;
+      }
+      const float inv_k = 1.0f / (float)K;
+      float mean = 0.f, var = t2 * inv_k;
+      if (NORM == 2) {
+        mean = t1 * inv_k;
+        var = fmaxf(var - mean * mean, 0.f);
+      }
+      const float rstd = rsqrtf(var + a.eps);
+      T* yrow = a.out_y ? static_cast<T*>(a.out_y) + (r0 + r) * a.ld_y : nullptr;
+      for (int v = v0 + lane; v < v1; v += 32) {
+        const uint4 d = lds_u128(row_a + (uint32_t)v * 16u);
+        const uint4 wv = lds_u128(w_sm + (uint32_t)v * 16u);
+        const uint32_t xd[4] = {d.x, d.y, d.z, d.w}, wd[4] = {wv.x, wv.y, wv.z, wv.w};
+        uint32_t yd[4];
+        if (NORM == 1) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const uint32_t h0 = Pk<T>::from_f(__fmul_rn(Pk<T>::to_f(xd[j] & 0xFFFFu), rstd));
+            const uint32_t h1 = Pk<T>::from_f(__fmul_rn(Pk<T>::to_f(xd[j] >> 16), rstd));
+            yd[j] = pmul<V2>(h0 | (h1 << 16), wd[j]);             // rn_T(w * h): one rounding, as the fp32 product
+          }
+        } else {
+          const uint4 bv = b_sm ? lds_u128(b_sm + (uint32_t)v * 16u) : make_uint4(0u, 0u, 0u, 0u);
+          const uint32_t bd[4] = {bv.x, bv.y, bv.z, bv.w};
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const float n0 = __fmul_rn(Pk<T>::to_f(xd[j] & 0xFFFFu) - mean, rstd);
+            const float n1 = __fmul_rn(Pk<T>::to_f(xd[j] >> 16) - mean, rstd);
+            const uint32_t y0 = Pk<T>::from_f(fmaf(n0, Pk<T>::to_f(wd[j] & 0xFFFFu), Pk<T>::to_f(bd[j] & 0xFFFFu)));
+            const uint32_t y1 = Pk<T>::from_f(fmaf(n1, Pk<T>::to_f(wd[j] >> 16), Pk<T>::to_f(bd[j] >> 16)));
+            yd[j] = y0 | (y1 << 16);
+          }
+        }
+        const uint4 yv = make_uint4(yd[0], yd[1], yd[2], yd[3]);
+        sts_u128(row_a + (uint32_t)v * 16u, yv);
+        if (yrow) *reinterpret_cast<uint4*>(yrow + (int64_t)v * 8) = yv;
+      }
+    }
+  }
+}
+
+template <typename T, bool GATHER, int NORM = 0>
 __global__ void __launch_bounds__(kThreadsH2, 1)
 quant_rows_h2(const H2Args a) {
   using V2 = typename Pk<T>::V2;
@@ -154,10 +254,16 @@ quant_rows_h2(const H2Args a) {
   // shared memory: [full[3] empty[3] | pad to 128][tbl u16 x 2^mant][ssal u16 x sal_cols][rows ...]
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem);
   uint64_t* empty_bar = full_bar + kStagesH2;
+  uint64_t* norm_bar = empty_bar + kStagesH2;                            // NORM: rows of the stage are normalised
   uint16_t* tbl = reinterpret_cast<uint16_t*>(smem + 128);
   constexpr int kTbl = 1 << Pk<T>::kMant;
   uint16_t* ssal = tbl + kTbl;
-  const size_t rows_off = (128 + (size_t)kTbl * 2 + (size_t)q.sal_cols * 2 + 127) / 128 * 128;
+  size_t rows_off = (128 + (size_t)kTbl * 2 + (size_t)q.sal_cols * 2 + 127) / 128 * 128;
+  // NORM: [psum float2 x kNormMaxRows][norm weight T x K][norm bias T x K] in front of the rows
+  float2* psum = reinterpret_cast<float2*>(smem + rows_off);
+  const uint32_t w_sm = smem_u32(smem + rows_off + kNormMaxRows * 8);
+  const uint32_t b_sm = (NORM == 2 && a.norm_b) ? w_sm + (uint32_t)K * 2u : 0u;
+  if (NORM) rows_off += (kNormMaxRows * 8 + (size_t)K * 2 * (NORM == 2 ? 2 : 1) + 127) / 128 * 128;
   unsigned char* srows = smem + rows_off;
   const uint32_t srows_a = smem_u32(srows);
   const uint32_t stage_b = (uint32_t)a.rps * pitch_b;
@@ -170,10 +276,17 @@ quant_rows_h2(const H2Args a) {
     for (int s = 0; s < kStagesH2; ++s) {
       mbar_init(&full_bar[s], 1);
       mbar_init(&empty_bar[s], kConsWarps + 1);
+      mbar_init(&norm_bar[s], kConsWarps);
     }
     fence_mbar_init();
   }
   for (int m = tid; m < kTbl; m += blockDim.x) tbl[m] = rcp_mant_entry<T>(m);
+  if (NORM) {                                                     // norm weight (+ bias): K * 2 bytes each, K % 8 == 0
+    for (int v = tid; v < (K >> 3); v += blockDim.x) {
+      sts_u128(w_sm + (uint32_t)v * 16u, __ldg(reinterpret_cast<const uint4*>(a.norm_w) + v));
+      if (b_sm) sts_u128(b_sm + (uint32_t)v * 16u, __ldg(reinterpret_cast<const uint4*>(a.norm_b) + v));
+    }
+  }
   for (int j = tid; j < q.sal_cols; j += blockDim.x)
     ssal[j] = j < q.Ks ? (uint16_t)(q.sal[j] * 2) : (uint16_t)zero_off;
   {  // zero everything behind the K copied elements of every staged row (never written by the bulk copies)
@@ -210,6 +323,7 @@ quant_rows_h2(const H2Args a) {
         issue(nx);
       }
       if (!mbar_wait(&full_bar[s], (uint32_t)((i / kStagesH2) & 1), 0x110u + s)) return;
+      if (NORM && !mbar_wait(&norm_bar[s], (uint32_t)((i / kStagesH2) & 1), 0x130u + s)) return;
       if (q.sal_cols > 0) {
         const int64_t r0 = (my_first + i * gridDim.x) * a.rps;
         const int nr = (int)min((int64_t)a.rps, q.R - r0);
@@ -274,6 +388,13 @@ quant_rows_h2(const H2Args a) {
     const int64_t r0 = (my_first + i * gridDim.x) * a.rps;
     const int nr = (int)min((int64_t)a.rps, q.R - r0);
     const uint32_t sbase = srows_a + (uint32_t)s * stage_b;
+    if (NORM) {
+      norm_stage<T, NORM>(a, sbase, pitch_b, nr, r0, K, w_sm, b_sm, psum, warp, lane);
+      fence_proxy_async_smem();     // the next bulk copy into this stage is ordered after these generic-proxy stores
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&norm_bar[s]);
+      if (!mbar_wait(&norm_bar[s], (uint32_t)((i / kStagesH2) & 1), 0x138u + s)) return;
+    }
 
     int row = row0, u = u0;
     for (int ii = 0; ii < n_iter; ++ii) {
@@ -366,9 +487,10 @@ struct H2Plan {
 };
 
 template <typename T>
-H2Plan plan_h2(const QuantArgs& q, int n_bits, int x_blocks, int64_t blk_cols, int64_t blk_stride) {
+H2Plan plan_h2(const QuantArgs& q, int n_bits, int x_blocks, int64_t blk_cols, int64_t blk_stride, int norm = 0) {
   H2Plan p{};
   p.ok = false;
+  if (norm && (x_blocks > 1 || q.K > 16384)) return p;
   if (sizeof(T) != 2) return p;
   const int g = q.g;
   if (g < 32 || g > 1024 || (g & (g - 1)) != 0) return p;
@@ -395,7 +517,8 @@ H2Plan plan_h2(const QuantArgs& q, int n_bits, int x_blocks, int64_t blk_cols, i
   const size_t row_bytes = (size_t)a.pitch * 2;
   const int vec = 8;
   a.q.sal_cols = q.Ks > 0 ? (int)((q.sal_width + vec - 1) / vec * vec) : 0;
-  const size_t fixed = 128 + (size_t)(1 << Pk<T>::kMant) * 2 + (size_t)a.q.sal_cols * 2 + 256;
+  const size_t fixed = 128 + (size_t)(1 << Pk<T>::kMant) * 2 + (size_t)a.q.sal_cols * 2 + 256 +
+                       (norm ? kNormMaxRows * 8 + (size_t)q.K * 2 * (norm == 2 ? 2 : 1) + 128 : 0);
   const size_t budget = 226 * 1024;
   if (fixed + (size_t)kStagesH2 * row_bytes > budget) return p;
   int fit = (int)((budget - fixed) / ((size_t)kStagesH2 * row_bytes));
@@ -418,6 +541,13 @@ H2Plan plan_h2(const QuantArgs& q, int n_bits, int x_blocks, int64_t blk_cols, i
   if ((size_t)a.rps * q.K * 2 >= (1u << 20)) return p;          // mbarrier tx-count limit
   p.smem = fixed / 128 * 128 + 128 + (size_t)kStagesH2 * a.rps * row_bytes;
   if (p.smem > 227 * 1024) return p;
+  a.norm = norm;
+  if (norm) {
+    if (a.rps > kNormMaxRows) return p;
+    int parts = 1;
+    while (parts * 2 * a.rps <= kConsWarps) parts *= 2;           // consumer warps sharing a row in the norm phase
+    a.norm_parts = parts;
+  }
   p.ok = true;
   return p;
 }
@@ -434,6 +564,8 @@ int launch_h2(const H2Plan& p, cudaStream_t st) {
     MQ_CHECK_CUDA(cudaGetLastError());
     return MQ_OK;
   };
+  if (a.norm == 1) return p.gather ? go(quant_rows_h2<T, true, 1>) : go(quant_rows_h2<T, false, 1>);
+  if (a.norm == 2) return p.gather ? go(quant_rows_h2<T, true, 2>) : go(quant_rows_h2<T, false, 2>);
   return p.gather ? go(quant_rows_h2<T, true>) : go(quant_rows_h2<T, false>);
 }
 

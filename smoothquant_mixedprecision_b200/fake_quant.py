@@ -166,8 +166,9 @@ def _version_of(t):
         return None
 
 
-def _shared_act(x_orig, xin, mod):
-    """K1 output for `xin` (= x_orig as a 2-D tensor of the compute dtype), shared within a group of layers."""
+def _shared_act(x_orig, xin, mod, producer=None):
+    """K1 output for `xin` (= x_orig as a 2-D tensor of the compute dtype), shared within a group of layers.
+    ``producer(perm, sal)``: what to run instead of ops.quant_rows on a miss (the fused norm + quantiser)."""
     pid = getattr(mod, "_partition_id", None)
     share = getattr(mod, "_share_n", None)
     dev = xin.device
@@ -185,13 +186,92 @@ def _shared_act(x_orig, xin, mod):
                         del _ACT_CACHE["entries"][slot]
                 return a
     perm, sal = mod.exec_partition()
-    a = ops.quant_rows(xin, perm, sal, mod.group_size, mod.quant_bits,
-                       Kn=0 if mod.perm is None else mod.perm.numel(), int_groups=mod.int_groups)
+    if producer is not None:
+        a = producer(perm, sal)
+    else:
+        a = ops.quant_rows(xin, perm, sal, mod.group_size, mod.quant_bits,
+                           Kn=0 if mod.perm is None else mod.perm.numel(), int_groups=mod.int_groups)
     if pid is not None and (share is None or share > 1):
         with _ACT_LOCK:
             _ACT_CACHE["entries"][slot] = {"x": x_orig, "xin": xin, "sig": sig, "a": a,
                                            "left": None if share is None else share - 1}
     return a
+
+
+class NormedRows:
+    """Lazy output of a FusedNorm: the norm's INPUT plus the norm itself.  A mode="fused" W4A4Linear consumes it
+    through mq_norm_quant_rows (norm + quantise in one pass over x); anything else calls
+    ``materialize()``.  Carries just enough of the tensor interface (shape / size / dim / dtype / device) for the
+    attention and MLP blocks of transformers' Llama / Mistral / OPT to pass it on to their linears."""
+
+    def __init__(self, x, norm, kind):
+        self.x, self.norm, self.kind = x, norm, kind
+        self._y = None
+
+    @property
+    def shape(self):
+        return self.x.shape
+
+    @property
+    def dtype(self):
+        return self.x.dtype
+
+    @property
+    def device(self):
+        return self.x.device
+
+    def dim(self):
+        return self.x.dim()
+
+    def size(self, *a):
+        return self.x.size(*a)
+
+    def is_inference(self):
+        return self.x.is_inference()
+
+    @property
+    def _version(self):
+        return self.x._version
+
+    @property
+    def eps(self):
+        return float(getattr(self.norm, "variance_epsilon", getattr(self.norm, "eps", 1e-6)))
+
+    def materialize(self):
+        if self._y is None:
+            self._y = self.norm(self.x)
+        return self._y
+
+
+class FusedNorm(nn.Module):
+    """Stands in for the RMSNorm / LayerNorm in front of a group of mode="fused" W4A4 linears that share one K
+    partition (q/k/v behind input_layernorm, gate/up behind post_attention_layernorm; smooth.py:126-141): returns a
+    NormedRows for 16-bit CUDA inputs, the plain norm output otherwise."""
+
+    def __init__(self, norm, kind):
+        super().__init__()
+        _check_choice(kind, ("rms", "layer"), "norm kind")
+        self.norm, self.kind = norm, kind
+
+    def forward(self, x):
+        if x.is_cuda and x.dtype in (torch.float16, torch.bfloat16) and x.shape[-1] % 8 == 0 and x.dim() in (2, 3) \
+                and (self.kind == "rms" or tuple(self.norm.normalized_shape) == (x.shape[-1],)):
+            return NormedRows(x, self.norm, self.kind)
+        return self.norm(x)
+
+
+def fuse_norm_(parent, norm_attr, consumers, kind):
+    """Replace ``parent.<norm_attr>`` by a FusedNorm when every consumer is a packed mode="fused" W4A4Linear with the
+    same partition on the integer engine (otherwise the norm would be recomputed per consumer).  Returns True if
+    fused."""
+    norm = getattr(parent, norm_attr, None)
+    if norm is None or isinstance(norm, FusedNorm) or getattr(norm, "weight", None) is None:
+        return False
+    ok = all(isinstance(c, W4A4Linear) and c.mode == "fused" and c._norm_fusable() for c in consumers)
+    if not ok or len({getattr(c, "_partition_id", None) for c in consumers}) != 1:
+        return False
+    setattr(parent, norm_attr, FusedNorm(norm, kind))
+    return True
 
 
 def _validate_columns(idx, K, what):
@@ -373,6 +453,8 @@ class W4A4Linear(nn.Module):
     def forward(self, x, act_perm=None, out_perm=None):
         if isinstance(x, parallel.BlockedColumns):      # gathered output of a column-parallel producer, [p, M, S]
             return self._forward_blocked_input(x)
+        if isinstance(x, NormedRows):                   # the producing norm is fused into the row quantiser
+            return self._forward_normed(x, act_perm, out_perm)
         shape = x.shape
         if x.dim() == 3:
             x2 = x.reshape(-1, shape[-1])
@@ -396,6 +478,38 @@ class W4A4Linear(nn.Module):
         if y.dtype != x2.dtype:
             y = y.to(x2.dtype)
         return y.view(shape[0], shape[1], -1) if x.dim() == 3 else y
+
+    def _norm_fusable(self):
+        g = self.group_size
+        G = 0 if self.perm is None else (self.perm.numel() + g - 1) // g
+        return (self.w_codes is not None or self.w_decode is not None) and G >= 1 and 32 <= g <= 1024 \
+            and g & (g - 1) == 0 and (self.int_groups is None or self.int_groups == G) and self.quant_bits <= 7 \
+            and 256 <= self.in_features <= 16384 and self.in_features % 8 == 0
+
+    def _forward_normed(self, nx, act_perm=None, out_perm=None):
+        x = nx.x
+        cdt = self.w_sal.dtype if self.w_sal is not None else (
+            self.w_decode.dtype if self.w_decode is not None else x.dtype)
+        if self.mode != "fused" or not self._norm_fusable() or x.dtype != cdt or act_perm is not None \
+                or x.shape[-1] != self.in_features:
+            return self.forward(nx.materialize(), act_perm, out_perm)
+        x2 = x.reshape(-1, x.shape[-1])
+        w, b = nx.norm.weight, getattr(nx.norm, "bias", None)
+        kn = self.perm.numel()
+
+        def producer(perm, sal):
+            return ops.norm_quant_rows(x2, w, b, nx.eps, nx.kind, perm, sal, self.group_size, self.quant_bits, Kn=kn)
+
+        if self._emits_blocked() and x.dim() == 2:
+            return self._forward_fused(nx, x2, blocked_out=True, producer=producer)
+        y = self._forward_fused(nx, x2, producer=producer)
+        if self.tp_world > 1 and self.tp_gather_output:
+            y = parallel.gather_columns(y, self.full_out_features, self.tp_group)
+        if self.output_quant_name != "None":
+            y = self._quantize_output(y, out_perm)
+        if y.dtype != x.dtype:
+            y = y.to(x.dtype)
+        return y.view(*x.shape[:-1], -1) if x.dim() == 3 else y
 
     def _emits_blocked(self):
         return (self.tp_world > 1 and self.tp_gather_output and getattr(self, "tp_blocked_output", False)
@@ -452,7 +566,7 @@ class W4A4Linear(nn.Module):
         self.tp_blocked_output = bool(blocked_output)
         return self
 
-    def _forward_fused(self, x, x2, blocked_out=False):
+    def _forward_fused(self, x, x2, blocked_out=False, producer=None):
         cdt = self.w_sal.dtype if self.w_sal is not None else (self.w_decode.dtype if self.w_decode is not None else (
             x2.dtype if x2.dtype in (torch.float16, torch.bfloat16) else torch.float16))
         xin = x2 if x2.dtype == cdt else x2.to(cdt)
@@ -461,18 +575,18 @@ class W4A4Linear(nn.Module):
             peer = parallel.peer_gather_for(self.tp_group)
             if peer is not None:                # copy engines over peer-mapped memory (parallel.PeerGather)
                 slot = peer.buffer(x2.shape[0], self.full_out_features, cdt)
-                self._fused_gemm(x, xin, cdt, out=slot["buf"][self.tp_rank])
+                self._fused_gemm(x, xin, cdt, out=slot["buf"][self.tp_rank], producer=producer)
                 return peer.gather(slot, self.full_out_features, parallel.ASYNC_GATHER)
             buf = parallel.gather_buffer(x2.shape[0], self.full_out_features, self.tp_world, cdt, x2.device)
-            y = self._fused_gemm(x, xin, cdt, out=buf[self.tp_rank])
+            y = self._fused_gemm(x, xin, cdt, out=buf[self.tp_rank], producer=producer)
             return parallel.gather_columns_blocked(buf[self.tp_rank][:, : y.shape[1]], self.full_out_features,
                                                    self.tp_group, buf=buf)
-        return self._fused_gemm(x, xin, cdt)
+        return self._fused_gemm(x, xin, cdt, producer=producer)
 
-    def _fused_gemm(self, x, xin, cdt, out=None):
+    def _fused_gemm(self, x, xin, cdt, out=None, producer=None):
         # layers fed by the same tensor with the same K partition (q/k/v, gate/up: same calibration statistics in
         # the reference, fake_quant.py:396-455) share one quantised activation
-        a = _shared_act(x, xin, self)
+        a = _shared_act(x, xin, self, producer)
         # weight-bandwidth regime: int4-resident weights.  Up to DECODE_PREFER_TOKENS the decode kernel wins outright;
         # between that and DECODE_MAX_TOKENS it is only taken when the prefill operand is not resident
         if self.w_decode is not None and (a.rows <= ops.DECODE_PREFER_TOKENS or (
@@ -854,6 +968,13 @@ def quantize_opt(model, weight_quant="per_tensor", act_quant="per_tensor", quant
             _swap(m, "out_proj", prefix, input_feat, False, False, kw, extra)
             _mark_shared(m, ("q_proj", "k_proj", "v_proj"))
             _mark_shared(m, ("out_proj",))
+    if extra.get("fuse_norm") and extra.get("mode") == "fused":
+        # pre-norm OPT: self_attn_layer_norm -> q/k/v, final_layer_norm -> fc1 (smooth.py:144-156)
+        for m in model.model.modules():
+            if isinstance(m, OPTDecoderLayer) and getattr(m, "do_layer_norm_before", False):
+                fuse_norm_(m, "self_attn_layer_norm", [m.self_attn.q_proj, m.self_attn.k_proj, m.self_attn.v_proj],
+                           "layer")
+                fuse_norm_(m, "final_layer_norm", [m.fc1], "layer")
     return model
 
 
@@ -879,6 +1000,13 @@ def quantize_llama_like(model, weight_quant="per_channel", act_quant="per_token"
             _swap(m, "o_proj", prefix, input_feat, True, False, kw, extra)
             _mark_shared(m, ("q_proj", "k_proj", "v_proj"))
             _mark_shared(m, ("o_proj",))
+    if extra.get("fuse_norm") and extra.get("mode") == "fused":
+        # input_layernorm -> q/k/v and post_attention_layernorm -> gate/up (smooth.py:126-141)
+        for m in model.model.modules():
+            attn, mlp = getattr(m, "self_attn", None), getattr(m, "mlp", None)
+            if attn is not None and mlp is not None and hasattr(m, "input_layernorm"):
+                fuse_norm_(m, "input_layernorm", [attn.q_proj, attn.k_proj, attn.v_proj], "rms")
+                fuse_norm_(m, "post_attention_layernorm", [mlp.gate_proj, mlp.up_proj], "rms")
     return model
 
 

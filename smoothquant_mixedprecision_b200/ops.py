@@ -257,6 +257,57 @@ def unpack_int4(packed: torch.Tensor, out: Optional[torch.Tensor] = None) -> tor
     return out
 
 
+NORM_KINDS = {"rms": 1, "layer": 2}
+
+
+def norm_quant_rows(x: torch.Tensor, norm_weight: torch.Tensor, norm_bias: Optional[torch.Tensor], eps: float,
+                    kind: str, perm: Optional[torch.Tensor], sal: Optional[torch.Tensor], group_size: int,
+                    n_bits: int = 4, Kn: Optional[int] = None, want_y: bool = False):
+    """RMSNorm / LayerNorm fused into the row quantiser (mq_norm_quant_rows): x [*, K] is read once,
+    the normalised row only ever lives in shared memory.  Returns the QuantizedRows of norm(x) (what quant_rows would
+    return for the normalised tensor, bit for bit given the same normalised values) and, with ``want_y``, the
+    normalised rows themselves.  Anchors: smooth.py:126-141 (which norm feeds which linears), fake_quant.py:78-101."""
+    _need_cuda(x, norm_weight, norm_bias, perm, sal)
+    if kind not in NORM_KINDS:
+        raise ValueError(f"Invalid norm kind: {kind}")
+    x2 = _rows2d(x)
+    if x2.dtype not in (torch.float16, torch.bfloat16):
+        raise TypeError("norm_quant_rows computes on float16 / bfloat16 rows")
+    R, K = x2.shape
+    dev = x.device
+    perm, sal = _i32(perm, dev), _i32(sal, dev)
+    if Kn is None:
+        Kn = perm.numel() if perm is not None else K
+    Ks = 0 if sal is None else sal.numel()
+    g = int(group_size)
+    G = (Kn + g - 1) // g
+    w = norm_weight.to(device=dev, dtype=x2.dtype).contiguous()
+    b = None if norm_bias is None else norm_bias.to(device=dev, dtype=x2.dtype).contiguous()
+    ld_codes = max(_round_up(G * g, 128), 128)
+    ld_scales = max(_round_up(R, 4), 4)
+    ld_sal = _round_up(Ks, 8)
+    codes = torch.empty((R, ld_codes), dtype=torch.int8, device=dev)
+    scales = torch.empty((max(G, 1), ld_scales), dtype=torch.float32, device=dev)
+    sal_out = torch.empty((R, ld_sal), dtype=x2.dtype, device=dev) if Ks > 0 else None
+    y = torch.empty((R, K), dtype=x2.dtype, device=dev) if want_y else None
+    ev = None
+    if QUANT_EVENTS is not None:
+        ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+        ev[0].record(torch.cuda.current_stream(dev))
+    with torch.cuda.device(dev):
+        check(lib.mq_norm_quant_rows(x2.data_ptr(), R, K, _ld(x2), _dtype_code(x2), NORM_KINDS[kind], w.data_ptr(),
+                                     _ptr(b), float(eps), _ptr(perm), Kn, _ptr(sal), Ks, g, n_bits, codes.data_ptr(),
+                                     ld_codes, scales.data_ptr(), ld_scales, _ptr(sal_out), ld_sal, _ptr(y), K,
+                                     _stream(x)), "mq_norm_quant_rows")
+    if ev is not None:
+        ev[1].record(torch.cuda.current_stream(dev))
+        QUANT_EVENTS.append((ev[0], ev[1], R * K * x2.element_size() + R * G * g + G * R * 4
+                             + R * ld_sal * x2.element_size() + (R * K * x2.element_size() if want_y else 0)))
+    a = QuantizedRows(codes=codes, scales=scales[:G], sal=sal_out, rows=R, Kn=Kn, Ks=Ks, group_size=g, int_groups=G,
+                      n_salient=Ks)
+    return (a, y) if want_y else a
+
+
 # ---------------------------------------------------------------------------------------------- K2
 def mixed_gemm(a: Optional[QuantizedRows], w: Optional[QuantizedRows], bias: Optional[torch.Tensor],
                a_sal: Optional[torch.Tensor] = None, w_sal: Optional[torch.Tensor] = None,

@@ -398,3 +398,52 @@ def test_folded_mlp_permutation_is_bit_identical(fq, golden_models):
         assert torch.equal(back(ids).logits, lf)
     assert all(mod.input_folded for n, mod in back.named_modules() if n.endswith("down_proj"))
     fq.clear_act_cache()
+
+
+@pytest.mark.parametrize("kind", ["llama", "opt"])
+def test_fused_norm_walker_option(fq, kind):
+    """quantize_*(..., mode="fused", fuse_norm=True): the norms in front of q/k/v and gate/up (fc1) become FusedNorm,
+    the linears behind them run mq_norm_quant_rows, and the model's logits stay within a small relative distance of
+    the unfused model's (the two differ by the rare last-place differences of the norm, see test_ops_gpu)."""
+    import copy
+    from transformers import LlamaConfig, LlamaForCausalLM, OPTConfig, OPTForCausalLM
+    import oracle_modules as OM
+    from smoothquant_mixedprecision_b200 import ops
+    torch.manual_seed(5)
+    if kind == "llama":
+        base = LlamaForCausalLM(LlamaConfig(vocab_size=128, hidden_size=256, intermediate_size=704, num_hidden_layers=2,
+                                            num_attention_heads=4, num_key_value_heads=4, max_position_embeddings=64))
+        walker = fq.quantize_llama_like
+    else:
+        base = OPTForCausalLM(OPTConfig(vocab_size=128, hidden_size=256, ffn_dim=1024, num_hidden_layers=2,
+                                        num_attention_heads=4, max_position_embeddings=64, word_embed_proj_dim=256))
+        walker = fq.quantize_opt
+    base = base.half().eval().to(DEV)
+    gen = torch.Generator().manual_seed(1)
+    calib = [torch.randint(3, 128, (2, 32), generator=gen).to(DEV)]
+    ids = torch.randint(3, 128, (2, 48), generator=gen).to(DEV)
+    feat = OM.hook_input_feat(base, calib)
+    with torch.no_grad():
+        fp = base(ids).logits.float()
+    plain, fused = copy.deepcopy(base), copy.deepcopy(base)
+    kw = dict(weight_quant="per_group", act_quant="per_group", input_feat=feat, salient_prop=0.05, group_size=64,
+              mode="fused", int_fraction=1.0, quantize_bmm_input=False)
+    walker(plain, **kw)
+    walker(fused, fuse_norm=True, **kw)
+    n_fused = sum(isinstance(m, fq.FusedNorm) for m in fused.modules())
+    assert n_fused == 4 and not any(isinstance(m, fq.FusedNorm) for m in plain.modules())
+    calls = []
+    real = ops.norm_quant_rows
+    ops.norm_quant_rows = lambda *a, **k: (calls.append(1), real(*a, **k))[1]
+    try:
+        with torch.no_grad():
+            got = fused(ids).logits.float()
+    finally:
+        ops.norm_quant_rows = real
+    assert len(calls) == 4                      # one fused quantiser per norm: q/k/v and gate/up share it
+    with torch.no_grad():
+        want = plain(ids).logits.float()
+    noise = float((want - fp).norm() / fp.norm())
+    rel = float((got - want).norm() / want.norm())
+    assert rel < 0.25 * noise + 1e-3, (rel, noise)
+    fq.clear_act_cache()

@@ -540,3 +540,68 @@ def test_decode_layer_releases_prefill_codes_and_rebuilds_them(ops, g):
     with pytest.raises(ValueError):
         fq.W4A4Linear.from_float(lin, "per_group", "per_group", group_size=32, mode="fused").prepare_decode()
     fq.clear_act_cache()
+
+
+def _torch_norm(x, w, b, eps, kind):
+    """What the model runs in front of the linears: transformers' LlamaRMSNorm.forward / F.layer_norm."""
+    if kind == "rms":
+        h = x.float()
+        h = h * torch.rsqrt(h.pow(2).mean(-1, keepdim=True) + eps)
+        return w * h.to(x.dtype)
+    return torch.nn.functional.layer_norm(x, (x.shape[-1],), w, b, eps)
+
+
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("kind", ["rms", "layer"])
+@pytest.mark.parametrize("M,K,g,p", [(300, 4096, 128, 0.05), (77, 768, 64, 0.05), (1024, 5120, 128, 0.10),
+                                     (33, 8192, 1024, 0.0), (4096, 2048, 32, 0.05)])
+def test_norm_quant_rows_is_norm_then_row_quantiser(ops, M, K, g, p, kind, dtype):
+    """mq_norm_quant_rows.  Floating-point part: the normalised rows equal the torch norm on all but a
+    sliver of the elements and differ there by last-place units of the 16-bit type -- the row statistic is an fp32 sum
+    in another order.  Integer part: codes, scales and the salient copy are those of the row quantiser / the oracle's group_quant
+    on the kernel's own normalised rows, bit for bit, with a permutation and in contiguous mode."""
+    from oracle import mq_oracle as O
+    torch.manual_seed(M + K)
+    x = (torch.randn(M, K, device=DEV) * torch.exp(0.5 * torch.randn(K, device=DEV)) + 0.3).to(dtype)
+    w = (1 + 0.2 * torch.randn(K, device=DEV)).to(dtype)
+    b = (0.1 * torch.randn(K, device=DEV)).to(dtype) if kind == "layer" else None
+    eps = 1e-6 if kind == "rms" else 1e-5
+    ks = int(round(K * p))
+    order = torch.randperm(K, device=DEV)
+    sal = torch.sort(order[:ks]).values.int() if ks else None
+    ref = _torch_norm(x, w, b, eps, kind)
+    for perm in (order[ks:].int(), None):
+        if perm is None:
+            Kn = K - ks
+            sal_c = torch.arange(Kn, K, device=DEV).int() if ks else None
+            a, y = ops.norm_quant_rows(x, w, b, eps, kind, None, sal_c, g, Kn=Kn, want_y=True)
+            want = ops.quant_rows(y, None, sal_c, g, 4, Kn=Kn)
+            cols, scol = torch.arange(Kn), sal_c
+        else:
+            a, y = ops.norm_quant_rows(x, w, b, eps, kind, perm, sal, g, want_y=True)
+            want = ops.quant_rows(y, perm, sal, g, 4)
+            cols, scol = perm.long().cpu(), sal
+        # floating point: a last-place difference of the inner rounding rn(x * rstd) times the norm weight is at most
+        # ~2 units in the last place of y; and the rows agree exactly on all but a sliver of the elements
+        ulp = torch.finfo(dtype).eps * torch.exp2(torch.floor(torch.log2(
+            ref.float().abs().clamp_min(torch.finfo(dtype).tiny))))
+        d = (y.float() - ref.float()).abs()
+        # (+ 2e-6 absolute: where w * n + b cancels to |y| << 1 the fp32 rounding noise of the O(1) terms is many ulps
+        # of the tiny result -- bf16 keeps 8 bits at any magnitude)
+        assert bool((d <= 3 * ulp + 2e-6).all()), float(((d - 2e-6) / ulp).max())
+        assert float((d > 0).float().mean()) < 5e-3, float((d > 0).float().mean())
+        # integer: the fused kernel quantises exactly like K1 on the same rows ...
+        G = want.groups
+        assert torch.equal(a.codes[:, : G * g], want.codes[:, : G * g])
+        assert torch.equal(a.scales[:, :M], want.scales[:, :M])
+        if ks:
+            assert torch.equal(a.sal[:, :ks], want.sal[:, :ks]) and torch.equal(a.sal[:, :ks], y[:, scol.long()])
+        # ... and like the reference quantiser (oracle) on sampled rows
+        rows = torch.arange(0, M, max(1, M // 16))[:16]
+        oq = O.group_quant(y[rows.to(DEV)].cpu()[:, cols], 4, g)
+        assert torch.equal(a.codes[rows.to(DEV)].cpu()[:, : G * g], oq.codes[:, : G * g])
+        assert torch.equal(a.scales[:G].cpu()[:, rows].t(), oq.scales.float())
+    # without want_y the result is the same
+    a2 = ops.norm_quant_rows(x, w, b, eps, kind, order[ks:].int(), sal, g)
+    a1, _ = ops.norm_quant_rows(x, w, b, eps, kind, order[ks:].int(), sal, g, want_y=True)
+    assert torch.equal(a2.codes, a1.codes) and torch.equal(a2.scales[:, :M], a1.scales[:, :M])

@@ -20,12 +20,22 @@ if contig:
 else:
     perm = order[ks:].int(); Kn = None
     sal = torch.sort(order[:ks]).values.int() if ks else None
-for _ in range(3): a = ops.quant_rows(x, perm, sal, g, Kn=Kn)
+norm = os.environ.get("MQ_NORM")          # rms | layer: the fused norm + quantiser; "unfused": torch RMSNorm, then K1
+w = (1 + 0.1 * torch.randn(K, device="cuda")).half()
+b = torch.zeros(K, device="cuda").half() if norm == "layer" else None
+def rms(t):
+    h = t.float(); h = h * torch.rsqrt(h.pow(2).mean(-1, keepdim=True) + 1e-6); return w * h.to(t.dtype)
+def run():
+    if norm in ("rms", "layer"): return ops.norm_quant_rows(x, w, b, 1e-6, norm, perm, sal, g, Kn=Kn)
+    if norm == "unfused": return ops.quant_rows(rms(x), perm, sal, g, Kn=Kn)
+    if norm == "unfused_layer": return ops.quant_rows(torch.nn.functional.layer_norm(x, (K,), w, w), perm, sal, g, Kn=Kn)
+    return ops.quant_rows(x, perm, sal, g, Kn=Kn)
+for _ in range(3): a = run()
 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 e0.record()
-for _ in range(20): a = ops.quant_rows(x, perm, sal, g, Kn=Kn)
+for _ in range(20): a = run()
 e1.record(); torch.cuda.synchronize()
 ms = e0.elapsed_time(e1) / 20
 G = a.scales.shape[0]
 nbytes = M * K * 2 + a.codes.numel() + G * M * 4 + (a.sal.numel() * 2 if a.sal is not None else 0)
-print("K1T " + json.dumps(dict(M=M, K=K, g=g, p=p, contig=contig, h2=os.environ.get('MQ_H2', '1'), ms=ms, gbs=nbytes / ms / 1e6)))
+print("K1T " + json.dumps(dict(M=M, K=K, g=g, p=p, contig=contig, h2=os.environ.get('MQ_H2', '1'), norm=norm, ms=ms, gbs=nbytes / ms / 1e6)))
