@@ -47,6 +47,11 @@ template <> struct Pk<__half> {
   static constexpr uint32_t kBias = 0u;              // low byte of bits(1536 + code) is the code itself
   __device__ static __forceinline__ float to_f(uint32_t lo16) { return __half2float(__ushort_as_half((unsigned short)lo16)); }
   __device__ static __forceinline__ uint32_t from_f(float v) { return __half_as_ushort(__float2half_rn(v)); }
+  __device__ static __forceinline__ float2 pair_f(uint32_t p) { return __half22float2(*reinterpret_cast<__half2*>(&p)); }
+  __device__ static __forceinline__ uint32_t pack_rn(float a, float b) {
+    const __half2 h = __floats2half2_rn(a, b);
+    return *reinterpret_cast<const uint32_t*>(&h);
+  }
 };
 template <> struct Pk<__nv_bfloat16> {
   using V2 = __nv_bfloat162;
@@ -57,6 +62,13 @@ template <> struct Pk<__nv_bfloat16> {
   static constexpr uint32_t kBias = 0x40u;           // 7-bit mantissa: low byte of bits(192 + code) is 64 + code
   __device__ static __forceinline__ float to_f(uint32_t lo16) { return __uint_as_float(lo16 << 16); }
   __device__ static __forceinline__ uint32_t from_f(float v) { return __bfloat16_as_ushort(__float2bfloat16_rn(v)); }
+  __device__ static __forceinline__ float2 pair_f(uint32_t p) {
+    return make_float2(__uint_as_float(p << 16), __uint_as_float(p & 0xFFFF0000u));
+  }
+  __device__ static __forceinline__ uint32_t pack_rn(float a, float b) {
+    const __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+    return *reinterpret_cast<const uint32_t*>(&h);
+  }
 };
 
 template <typename V2> __device__ __forceinline__ V2 as_v2(uint32_t u) { return *reinterpret_cast<V2*>(&u); }
@@ -173,19 +185,21 @@ __device__ __forceinline__ void norm_stage(const H2Args& a, uint32_t sbase, uint
     const bool have = r < nr;
     const uint32_t row_a = sbase + (uint32_t)min(r, a.rps - 1) * pitch_b;
     float s1 = 0.f, s2 = 0.f;
+    float2 q1 = make_float2(0.f, 0.f), q2 = make_float2(0.f, 0.f);
     if (have) {
       for (int v = v0 + lane; v < v1; v += 32) {
         const uint4 d = lds_u128(row_a + (uint32_t)v * 16u);
         const uint32_t wd[4] = {d.x, d.y, d.z, d.w};
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-          const float f0 = Pk<T>::to_f(wd[j] & 0xFFFFu), f1 = Pk<T>::to_f(wd[j] >> 16);
-          s2 = fmaf(f0, f0, s2);
-          s2 = fmaf(f1, f1, s2);
-          if (NORM == 2) s1 += f0 + f1;
+          const float2 f = Pk<T>::pair_f(wd[j]);
+          q2 = __ffma2_rn(f, f, q2);                     // two independent fp32 accumulators per lane
+          if (NORM == 2) q1 = __fadd2_rn(q1, f);
         }
       }
     }
+    s2 = q2.x + q2.y;
+    s1 = q1.x + q1.y;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
       s2 += __shfl_xor_sync(0xffffffffu, s2, o);
@@ -207,6 +221,7 @@ __device__ __forceinline__ void norm_stage(const H2Args& a, uint32_t sbase, uint
         var = fmaxf(var - mean * mean, 0.f);
       }
       const float rstd = rsqrtf(var + a.eps);
+      const float2 rstd2 = make_float2(rstd, rstd), nmean2 = make_float2(-mean, -mean);
       T* yrow = a.out_y ? static_cast<T*>(a.out_y) + (r0 + r) * a.ld_y : nullptr;
       for (int v = v0 + lane; v < v1; v += 32) {
         const uint4 d = lds_u128(row_a + (uint32_t)v * 16u);
@@ -216,20 +231,17 @@ __device__ __forceinline__ void norm_stage(const H2Args& a, uint32_t sbase, uint
         if (NORM == 1) {
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
-            const uint32_t h0 = Pk<T>::from_f(__fmul_rn(Pk<T>::to_f(xd[j] & 0xFFFFu), rstd));
-            const uint32_t h1 = Pk<T>::from_f(__fmul_rn(Pk<T>::to_f(xd[j] >> 16), rstd));
-            yd[j] = pmul<V2>(h0 | (h1 << 16), wd[j]);             // rn_T(w * h): one rounding, as the fp32 product
+            const float2 h = __fmul2_rn(Pk<T>::pair_f(xd[j]), rstd2);
+            yd[j] = pmul<V2>(Pk<T>::pack_rn(h.x, h.y), wd[j]);    // rn_T(w * h): one rounding, as the fp32 product
           }
         } else {
           const uint4 bv = b_sm ? lds_u128(b_sm + (uint32_t)v * 16u) : make_uint4(0u, 0u, 0u, 0u);
           const uint32_t bd[4] = {bv.x, bv.y, bv.z, bv.w};
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
-            const float n0 = __fmul_rn(Pk<T>::to_f(xd[j] & 0xFFFFu) - mean, rstd);
-            const float n1 = __fmul_rn(Pk<T>::to_f(xd[j] >> 16) - mean, rstd);
-            const uint32_t y0 = Pk<T>::from_f(fmaf(n0, Pk<T>::to_f(wd[j] & 0xFFFFu), Pk<T>::to_f(bd[j] & 0xFFFFu)));
-            const uint32_t y1 = Pk<T>::from_f(fmaf(n1, Pk<T>::to_f(wd[j] >> 16), Pk<T>::to_f(bd[j] >> 16)));
-            yd[j] = y0 | (y1 << 16);
+            const float2 n = __fmul2_rn(__fadd2_rn(Pk<T>::pair_f(xd[j]), nmean2), rstd2);
+            const float2 y = __ffma2_rn(n, Pk<T>::pair_f(wd[j]), Pk<T>::pair_f(bd[j]));
+            yd[j] = Pk<T>::pack_rn(y.x, y.y);
           }
         }
         const uint4 yv = make_uint4(yd[0], yd[1], yd[2], yd[3]);

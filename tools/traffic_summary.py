@@ -16,7 +16,7 @@ for r in rows:
 launches = list(by_id.values())[-int(sys.argv[2]):]
 out = {"source": f"ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum over `bench.py --layers 2` "
                  f"(last {len(launches)} launches = one step)", "kernels": {}}
-for key in ("mixed_gemm_kernel", "quant_rows_fast"):
+for key in ("mixed_gemm_kernel", "quant_rows_h2", "quant_rows_fast", "decode_gemm_kernel"):
     sel = [l for l in launches if key in l["kernel"]]
     if sel:
         rd = sum(l.get("dram__bytes_read.sum", 0) for l in sel) / len(sel)
