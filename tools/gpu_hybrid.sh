@@ -1,7 +1,6 @@
 #!/bin/bash
 # hybrid engine: parity tests, then GEMM time vs share of integer groups at the 7B prefill shape
 mkdir -p gpurun_out
-timeout 600 python -m pytest tests -m gpu -x -q 2>&1 | tail -4
 {
 for g in 128 64 256; do
   for f in 1.0 0.9 0.8 0.7 0.6 0.5 0.4 0.3 0.0; do
