@@ -331,8 +331,12 @@ def split_sequences(n_seq: int, world: int, rank: int) -> Tuple[int, int]:
 
 
 def layer_plan_llama() -> List[Tuple[str, bool]]:
-    """(linear name, gather_output) for one column-parallel Llama decoder layer: outputs are gathered only where the
-    consumer needs the full width: v->o and up->down feed K of the next linear, o/down feed the
-    residual stream; q/k feed per-head attention and gate feeds SiLU*mul, both column-local."""
+    """(linear name, gather_output) of the column-parallel plan bench.py times: a BYTE-COUNT PROXY of one decoder
+    layer, not a recipe for a real attention block.  The bench chains the 7 linears directly (v -> o, o -> gate/up,
+    up -> down), so the four tensors a pure column-parallel layer consumes at full width (attention
+    output [M, hidden], o_proj output, MLP intermediate [M, inter], down_proj output) are stood in for by the outputs
+    of v, o, up and down; q / k / gate stay column-local.  In a real model q, k and v are sharded over the same heads,
+    attention runs on the local heads and it is the ATTENTION OUTPUT that is gathered in front of o_proj (v_proj then
+    has gather_output=False), and act(gate) * up is formed on the local columns before it is gathered."""
     return [("q_proj", False), ("k_proj", False), ("v_proj", True), ("o_proj", True),
             ("gate_proj", False), ("up_proj", True), ("down_proj", True)]

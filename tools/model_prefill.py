@@ -56,7 +56,7 @@ def synthetic_calibration(model, dev, seed=1):
     return input_feat, scales
 
 
-def run(layers=32, batch=16, seq=2048, steps=3, warmup=2, quantize=True, dev="cuda:0"):
+def run(layers=32, batch=16, seq=2048, steps=3, warmup=2, quantize=True, dev="cuda:0", fold=False, fuse_norm=False):
     import torch
     from smoothquant_mixedprecision_b200 import ops
     from smoothquant_mixedprecision_b200.fake_quant import quantize_llama_like, W4A4Linear
@@ -68,7 +68,7 @@ def run(layers=32, batch=16, seq=2048, steps=3, warmup=2, quantize=True, dev="cu
         input_feat, act_scales = synthetic_calibration(model, dev)
         smooth_lm(model, act_scales, 0.85)
         quantize_llama_like(model, "per_group", "per_group", input_feat=input_feat, salient_prop=0.05, group_size=128,
-                            mode="fused", sort="max", sort_keys=act_scales)
+                            mode="fused", sort="max", sort_keys=act_scales, fold=fold, fuse_norm=fuse_norm)
         n_w4a4 = sum(isinstance(m, W4A4Linear) for m in model.modules())
         torch.cuda.empty_cache()
     setup_s = time.perf_counter() - t0
@@ -95,7 +95,7 @@ def run(layers=32, batch=16, seq=2048, steps=3, warmup=2, quantize=True, dev="cu
     gemm_ms = sum(a.elapsed_time(b) for a, b, _, _ in gev) / steps
     quant_ms = sum(a.elapsed_time(b) for a, b, _ in qev) / steps
     return {"workload": f"HF Llama-2-7B random-init ({layers} layers), smooth_lm alpha=0.85 + quantize_llama_like fused "
-                        f"g=128 5% salient, full forward {batch}x{seq} tokens" if quantize else
+                        f"g=128 5% salient (fold={fold}, fuse_norm={fuse_norm}), full forward {batch}x{seq} tokens" if quantize else
                         f"HF Llama-2-7B random-init ({layers} layers) fp16 nn.Linear (stock PyTorch), {batch}x{seq}",
             "tokens_per_s": batch * seq / (ms * 1e-3), "ms_per_step": ms, "w4a4_layers": n_w4a4,
             "w4a4_gemm_ms": gemm_ms, "w4a4_quant_ms": quant_ms,
@@ -110,8 +110,13 @@ def main():
     ap.add_argument("--seq", type=int, default=2048)
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--fp16-baseline", action="store_true", help="also time the un-quantised fp16 model")
+    ap.add_argument("--serving-options", action="store_true", help="also time fold=True, fuse_norm=True")
     args = ap.parse_args()
     print(json.dumps(run(args.layers, args.batch, args.seq, args.steps)), flush=True)
+    if args.serving_options:
+        import torch
+        torch.cuda.empty_cache()
+        print(json.dumps(run(args.layers, args.batch, args.seq, args.steps, fold=True, fuse_norm=True)), flush=True)
     if args.fp16_baseline:
         import torch
         torch.cuda.empty_cache()
