@@ -71,6 +71,11 @@ def parse():
                     help="tp: how gathered outputs travel -- peer = copy engines over peer-mapped memory, ordered by "
                          "stream memory operations (parallel.PeerGather, no SMs); nccl = all_gather_into_tensor; "
                          "auto = peer up to 4 GPUs, nccl beyond (measured: profiles/r02_tp_sweep.txt)")
+    ap.add_argument("--reserve-sms", type=int, default=None,
+                    help="tp over NCCL: SMs the persistent GEMM / row quantiser leave free so that the collective's "
+                         "kernel runs concurrently instead of queueing behind them (default 0: measured no gain, "
+                         "profiles/r02_tp_sweep.txt)")
+    ap.add_argument("--nccl-max-ctas", type=int, default=None, help="tp over NCCL: NCCL_MAX_CTAS (default: NCCL's own)")
     ap.add_argument("--peer-lanes", type=int, default=None, help="peer transport: copy streams pulling in parallel")
     ap.add_argument("--no-decode", action="store_true")
     return ap.parse_args()
@@ -375,6 +380,8 @@ def gpu_arm(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
+        if args.nccl_max_ctas is not None:
+            os.environ["NCCL_MAX_CTAS"] = str(args.nccl_max_ctas)
         dist.init_process_group("nccl", device_id=dev)
     M = args.tokens
     mode = args.parallel
@@ -499,11 +506,15 @@ def gpu_arm(args):
         dist.all_reduce(ok, op=dist.ReduceOp.MIN)
         if int(ok.item()) == 0:
             par.TRANSPORT, transport = "nccl", "nccl"
+        reserve = args.reserve_sms or 0
+        if reserve:
+            _lib.set_option("sm_reserve", reserve)
     stack, x0 = build_stack(args.layers, M, dev, seed=1234 + (0 if tp else rank), tp=(rank, world) if tp else None)
     job_tokens = M if tp else world * M
     main = measure(stack, x0, tp, True)
     other = None
     if world > 1 and args.parallel == "auto":           # the data-parallel figure beside the column-parallel headline
+        _lib.set_option("sm_reserve", 0)
         del stack
         torch.cuda.empty_cache()
         stack, x0 = build_stack(args.layers, M, dev, seed=1234 + rank, tp=None)
@@ -584,7 +595,8 @@ def gpu_arm(args):
         line["column_parallel"]["transport"] = (
             "peer-mapped memory: copy-engine pulls over NVLink ordered by stream memory operations (mq_peer_gather, "
             "no SMs); process group (NCCL) used for set-up and the timing barriers only" if transport == "peer"
-            else "NCCL all_gather_into_tensor, in place")
+            else f"NCCL all_gather_into_tensor, in place; NCCL_MAX_CTAS={os.environ.get('NCCL_MAX_CTAS', 'default')}, "
+                 f"{reserve} SMs left free by the persistent GEMM / row quantiser")
     if other is not None:
         line["data_parallel"] = {
             "value": world * M / (other["ms"] * 1e-3), "unit": "tokens/s", "scaling": "weak",

@@ -24,6 +24,7 @@ static MqOption g_options[] = {
     {"gemm_persistent", {0}}, {"quant_exact_div", {0}}, {"gemm_debug", {0}}, {"quant_force_generic", {0}},
     {"gemm_profile", {0}}, {"gemm_kernel", {0}}, {"gemm_pair", {0}}, {"gemm_magic_mma", {0}},
     {"quant_h2", {0}}, {"decode_bps", {0}}, {"decode_tpc", {0}}, {"decode_split", {0}},
+    {"sm_reserve", {0}},
 };
 
 int mq_get_option(const char* name, int dflt) {
@@ -33,6 +34,14 @@ int mq_get_option(const char* name, int dflt) {
       return v ? v : dflt;
     }
   return dflt;
+}
+
+// SMs the persistent kernels (prefill GEMM, row quantiser) may occupy: all of them minus option sm_reserve -- set when a
+// collective's kernel has to run concurrently (column-parallel over NCCL: its CTAs otherwise queue behind a persistent
+// GEMM that owns every SM).
+int mq_worker_sms() {
+  const int n = mq_sm_count(), r = mq_get_option("sm_reserve", 0);
+  return r > 0 && r < n - 2 ? n - r : n;
 }
 
 int mq_sm_count() {

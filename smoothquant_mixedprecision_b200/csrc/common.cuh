@@ -13,6 +13,7 @@
 void mq_set_error(const char* fmt, ...);
 int mq_get_option(const char* name, int dflt);
 int mq_sm_count();
+int mq_worker_sms();   // mq_sm_count() minus option sm_reserve
 
 #define MQ_CHECK_ARG(cond, ...)            \
   do {                                     \

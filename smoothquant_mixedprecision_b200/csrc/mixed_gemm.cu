@@ -744,7 +744,7 @@ int launch_gemm_m(const CUtensorMap& ma, const CUtensorMap& mw, const CUtensorMa
   p.tiles_m = (p.M + TM - 1) / TM;
   p.tiles_n = (p.N + BN - 1) / BN;
   const int64_t tiles = (int64_t)p.tiles_m * p.tiles_n;
-  const int64_t workers = kPair ? (int64_t)mq_sm_count() / 2 : (int64_t)mq_sm_count();
+  const int64_t workers = kPair ? (int64_t)mq_worker_sms() / 2 : (int64_t)mq_worker_sms();
   int64_t grid = mq_get_option("gemm_persistent", 0) == 2 ? tiles : workers;
   if (grid > tiles) grid = tiles;
   if (!kPair) {

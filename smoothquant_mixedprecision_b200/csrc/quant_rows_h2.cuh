@@ -568,7 +568,7 @@ template <typename T>
 int launch_h2(const H2Plan& p, cudaStream_t st) {
   const H2Args& a = p.args;
   const int64_t nblocks = (a.q.R + a.rps - 1) / a.rps;
-  int64_t grid = mq_sm_count();
+  int64_t grid = mq_worker_sms();
   if (grid > nblocks) grid = nblocks;
   auto go = [&](auto kern) -> int {
     MQ_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem));
