@@ -76,6 +76,9 @@ def parse():
                          "kernel runs concurrently instead of queueing behind them (default 0: measured no gain, "
                          "profiles/r02_tp_sweep.txt)")
     ap.add_argument("--nccl-max-ctas", type=int, default=None, help="tp over NCCL: NCCL_MAX_CTAS (default: NCCL's own)")
+    ap.add_argument("--peer-mode", default="pull", choices=["pull", "push", "mcast"],
+                    help="peer transport: pull peers' blocks, push the own block to every peer, or push once to the "
+                         "multicast address of the gather buffers")
     ap.add_argument("--peer-lanes", type=int, default=None, help="peer transport: copy streams pulling in parallel")
     ap.add_argument("--no-decode", action="store_true")
     return ap.parse_args()
@@ -498,7 +501,7 @@ def gpu_arm(args):
         transport = "nccl"
         if args.transport == "peer" or (args.transport == "auto" and world <= 4):
             try:
-                par.enable_peer_gather(lanes=args.peer_lanes)
+                par.enable_peer_gather(lanes=args.peer_lanes, mode=args.peer_mode)
                 transport = "peer"
             except Exception as e:      # no peer-mapped memory on this box: NCCL carries the gathers
                 print(f"bench.py: peer transport unavailable ({type(e).__name__}: {e}); using NCCL", file=sys.stderr)
@@ -593,8 +596,9 @@ def gpu_arm(args):
     if tp:
         line["column_parallel"] = main["comm"]
         line["column_parallel"]["transport"] = (
-            "peer-mapped memory: copy-engine pulls over NVLink ordered by stream memory operations (mq_peer_gather, "
-            "no SMs); process group (NCCL) used for set-up and the timing barriers only" if transport == "peer"
+            f"peer-mapped memory ({args.peer_mode}): copy-engine transfers over NVLink ordered by stream memory operations "
+            "(mq_peer_gather / mq_peer_push, no SMs); process group (NCCL) used for set-up and the timing barriers only"
+            if transport == "peer"
             else f"NCCL all_gather_into_tensor, in place; NCCL_MAX_CTAS={os.environ.get('NCCL_MAX_CTAS', 'default')}, "
                  f"{reserve} SMs left free by the persistent GEMM / row quantiser")
     if other is not None:

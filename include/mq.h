@@ -239,7 +239,7 @@ int mq_gemm_profile(unsigned long long* out_host, int n_ctas);
  * ordered by stream memory operations -- no kernel, so it runs underneath the persistent GEMM of the next chunk.
  *     bufs[world]   device address, in THIS process, of every rank's gather buffer [world][M][S]; the caller's GEMM
  *                   has written block `rank` of bufs[rank] in stream order before the call
- *     flags[world]  device address of every rank's flag block, uint32 [2][world] (ready, pulled), zero at start
+ *     flags[world]  device address of every rank's flag block, uint32 [4 + ring buffers][world], zero at start
  *     seq           1, 2, 3, ... : the same sequence of calls on every rank
  *     streams[n]    cudaStream_t handles (as integers): the peers are dealt round-robin over them so that several
  *                   copy engines pull in parallel; every one must already be ordered after the caller's GEMM
@@ -250,6 +250,17 @@ int mq_gemm_profile(unsigned long long* out_host, int n_ctas);
 int mq_peer_gather(const uint64_t* bufs, const uint64_t* flags, int rank, int world, size_t block_bytes,
                    uint32_t seq, const uint64_t* streams, int n_streams);
 int mq_peer_wait_pulled(const uint64_t* flags, int rank, int world, uint32_t seq, void* stream);
+/* Push variant of the same gather (flag block: uint32 [4 + ring buffers][world] = ready, pulled, arrived, unused, then
+ * one row consumed[buf_id] per ring buffer -- the gathers of ONE buffer are consumed in order).  mq_peer_push:
+ * once every peer has consumed gather `prev` (the previous user of this ring buffer; 0 = none), copy this rank's block
+ * into block `rank` of every peer's buffer -- or with ONE copy to mc_buf, the multicast address of the buffers, when
+ * mc_buf != 0 -- and publish arrived[rank] = seq.  mq_peer_wait_arrived: the stream that reads the gathered buffer waits
+ * for every peer's block.  mq_peer_publish_consumed: called on the compute stream before a ring buffer is reused. */
+int mq_peer_push(const uint64_t* bufs, const uint64_t* flags, uint64_t mc_buf, int rank, int world,
+                 size_t block_bytes, uint32_t seq, uint32_t prev, int buf_id, const uint64_t* streams,
+                 int n_streams);
+int mq_peer_wait_arrived(const uint64_t* flags, int rank, int world, uint32_t seq, void* stream);
+int mq_peer_publish_consumed(const uint64_t* flags, int rank, int world, uint32_t seq, int buf_id, void* stream);
 
 #ifdef __cplusplus
 }

@@ -47,6 +47,9 @@ SIGNATURES = {
     "mq_decode_gemm": (_i32, [_vp, _i64, _vp, _i64, _vp, _i64, _vp, _vp, _vp, _i64, _i64, _i64, _i32, _i64,
                               _i32, _vp, _i64, _vp]),
     "mq_peer_gather": (_i32, [_vp, _vp, _i32, _i32, _sz, C.c_uint32, _vp, _i32]),
+    "mq_peer_push": (_i32, [_vp, _vp, C.c_uint64, _i32, _i32, _sz, C.c_uint32, C.c_uint32, _i32, _vp, _i32]),
+    "mq_peer_wait_arrived": (_i32, [_vp, _i32, _i32, C.c_uint32, _vp]),
+    "mq_peer_publish_consumed": (_i32, [_vp, _i32, _i32, C.c_uint32, _i32, _vp]),
     "mq_peer_wait_pulled": (_i32, [_vp, _i32, _i32, C.c_uint32, _vp]),
     "mq_set_option": (_i32, [C.c_char_p, _i32]),
     "mq_quant_fault": (_i32, [C.POINTER(C.c_uint)]),

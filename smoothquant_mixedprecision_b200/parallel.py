@@ -201,7 +201,7 @@ class PeerGather:
     ``ring`` more gathers of the same shape have been issued (``dense()`` copies).  Every rank must issue the same
     sequence of gathers."""
 
-    def __init__(self, group=None, ring: int = 4, lanes: Optional[int] = None):
+    def __init__(self, group=None, ring: int = 4, lanes: Optional[int] = None, mode: str = "pull"):
         import ctypes as C
         import torch.distributed._symmetric_memory as symm
         from . import _lib
@@ -209,6 +209,11 @@ class PeerGather:
         self.group = group if group is not None else dist.group.WORLD
         self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
         self.ring = max(2, int(ring))
+        # pull: every rank copies its peers' blocks in (mq_peer_gather).  push: every rank copies its block out to every
+        # peer (mq_peer_push).  mcast: push with ONE copy to the multicast address of the buffers (NVSwitch replicates).
+        if mode not in ("pull", "push", "mcast"):
+            raise ValueError(f"Invalid peer gather mode: {mode}")
+        self.mode = mode
         self.dev = torch.device("cuda", torch.cuda.current_device())
         self.seq = 0
         self.rings = {}                       # (M, S, dtype) -> {"slots": [...], "next": i}
@@ -217,7 +222,9 @@ class PeerGather:
         self.lanes = max(1, min(self.world - 1, 1 if lanes is None else int(lanes)))
         self.streams = [torch.cuda.Stream(device=self.dev, priority=-1) for _ in range(self.lanes)]
         self._lane_ptrs = (C.c_uint64 * self.lanes)(*[s.cuda_stream for s in self.streams])
-        self.flags = symm.empty(max(64, 2 * self.world), dtype=torch.int32, device=self.dev)
+        self.max_buffers = 124                # rows of the consumed[buffer id] table behind the 4 fixed flag rows
+        self.n_buffers = 0
+        self.flags = symm.empty((4 + self.max_buffers) * self.world, dtype=torch.int32, device=self.dev)
         self.flags.zero_()
         self._fh = symm.rendezvous(self.flags, self.group)
         self._flag_ptrs = (C.c_uint64 * self.world)(*[int(p) for p in self._fh.buffer_ptrs])
@@ -234,7 +241,15 @@ class PeerGather:
             buf = self._symm.empty((self.world, M, S), dtype=dtype, device=self.dev)
             h = self._symm.rendezvous(buf, self.group)
             ptrs = (self._C.c_uint64 * self.world)(*[int(p) for p in h.buffer_ptrs])
-            slot = {"buf": buf, "h": h, "ptrs": ptrs, "last": 0}
+            mc = 0
+            if self.mode == "mcast":
+                if not h.has_multicast_support or not int(h.multicast_ptr):
+                    raise RuntimeError("peer gather mode 'mcast': no multicast mapping for the gather buffer")
+                mc = int(h.multicast_ptr)
+            if self.n_buffers >= self.max_buffers:
+                raise RuntimeError(f"peer gather: more than {self.max_buffers} ring buffers (distinct gather shapes)")
+            slot = {"buf": buf, "h": h, "ptrs": ptrs, "last": 0, "prev": 0, "mc": mc, "id": self.n_buffers}
+            self.n_buffers += 1
             ring["slots"].append(slot)
             return slot
         slot = ring["slots"][ring["next"]]
@@ -245,10 +260,16 @@ class PeerGather:
         """Next gather buffer of the ring for this shape; the current stream is made to wait until every peer has
         copied this rank's block of the buffer's previous gather out, so the GEMM may overwrite it."""
         slot = self._slot(M, shard_size(n_out, self.world), dtype)
+        slot["prev"] = slot["last"]
         if slot["last"]:
             st = torch.cuda.current_stream(self.dev).cuda_stream
-            self._lib.check(self._lib.lib.mq_peer_wait_pulled(self._flag_ptrs, self.rank, self.world, slot["last"], st),
-                            "mq_peer_wait_pulled")
+            if self.mode == "pull":
+                self._lib.check(self._lib.lib.mq_peer_wait_pulled(self._flag_ptrs, self.rank, self.world, slot["last"],
+                                                                  st), "mq_peer_wait_pulled")
+            else:       # everything queued on this stream so far -- the readers of the buffer's last gather -- is done
+                self._lib.check(self._lib.lib.mq_peer_publish_consumed(self._flag_ptrs, self.rank, self.world,
+                                                                       slot["last"], slot["id"], st),
+                                "mq_peer_publish_consumed")
         return slot
 
     def gather(self, slot: dict, n_out: int, async_op: bool = True) -> "BlockedColumns":
@@ -266,20 +287,40 @@ class PeerGather:
         start.record(cur)
         for s in self.streams:
             s.wait_event(start)
-        self._lib.check(self._lib.lib.mq_peer_gather(slot["ptrs"], self._flag_ptrs, self.rank, self.world, block,
-                                                     self.seq, self._lane_ptrs, self.lanes), "mq_peer_gather")
-        done = []
-        for s in self.streams:
-            e = torch.cuda.Event()
-            e.record(s)
-            done.append(e)
-        out = BlockedColumns(buf, n_out, _EventWork(done, self.dev))
+        if self.mode == "pull":
+            self._lib.check(self._lib.lib.mq_peer_gather(slot["ptrs"], self._flag_ptrs, self.rank, self.world, block,
+                                                         self.seq, self._lane_ptrs, self.lanes), "mq_peer_gather")
+            done = []
+            for s in self.streams:
+                e = torch.cuda.Event()
+                e.record(s)
+                done.append(e)
+            out = BlockedColumns(buf, n_out, _EventWork(done, self.dev))
+        else:
+            self._lib.check(self._lib.lib.mq_peer_push(slot["ptrs"], self._flag_ptrs, slot["mc"], self.rank, self.world,
+                                                       block, self.seq, slot["prev"], slot["id"], self._lane_ptrs,
+                                                       self.lanes),
+                            "mq_peer_push")
+            out = BlockedColumns(buf, n_out, _ArrivedWork(self, self.seq))
         if not async_op:
             out.wait()
             if ev is not None:
                 ev[1].record(cur)
                 COMM_EVENTS.append((ev[0], ev[1], (self.world - 1) * block))
         return out
+
+
+class _ArrivedWork:
+    """wait() = the current stream waits (stream memory operations, no kernel) until every peer's block of gather `seq`
+    has landed in this rank's buffer."""
+
+    def __init__(self, peer, seq):
+        self.peer, self.seq = peer, seq
+
+    def wait(self):
+        p = self.peer
+        st = torch.cuda.current_stream(p.dev).cuda_stream
+        p._lib.check(p._lib.lib.mq_peer_wait_arrived(p._flag_ptrs, p.rank, p.world, self.seq, st), "mq_peer_wait_arrived")
 
 
 class _EventWork:
@@ -298,13 +339,13 @@ _PEER = {}              # id(group) -> PeerGather
 TRANSPORT = "nccl"      # "peer": gathers of blocked-output layers go through PeerGather (set by enable_peer_gather)
 
 
-def enable_peer_gather(group=None, ring: int = 4, lanes: Optional[int] = None) -> PeerGather:
+def enable_peer_gather(group=None, ring: int = 4, lanes: Optional[int] = None, mode: str = "pull") -> PeerGather:
     """Collective: set up the peer-memory transport for `group` (one NVLink box) and make blocked-output layers use
     it.  Raises if symmetric memory cannot be established; the NCCL path stays available (TRANSPORT = "nccl")."""
     global TRANSPORT
     key = id(group) if group is not None else 0
-    if key not in _PEER:
-        _PEER[key] = PeerGather(group, ring, lanes)
+    if key not in _PEER or _PEER[key].mode != mode:
+        _PEER[key] = PeerGather(group, ring, lanes, mode)
     TRANSPORT = "peer"
     return _PEER[key]
 

@@ -216,9 +216,10 @@ def _nccl_pipeline_worker(rank, world, port):
         want = bench.run_stack(full, x0).clone()
         tpst, x1 = bench.build_stack(2, M, dev, seed=5, tp=(rank, world))
         assert torch.equal(x0, x1)
-        for transport, asynchronous in (("nccl", True), ("nccl", False), ("peer", True), ("peer", False)):
-            if transport == "peer":
-                P.enable_peer_gather(ring=3)
+        for transport, asynchronous in (("nccl", True), ("nccl", False), ("pull", True), ("pull", False),
+                                        ("push", True), ("push", False)):
+            if transport != "nccl":
+                P.enable_peer_gather(ring=3, mode=transport)
             P.ASYNC_GATHER = asynchronous
             for chunks in (1, 2, 3, 2, 1):      # the repeats re-use ring buffers (overwrite-after-pulled ordering)
                 rows = [(i * M // chunks, (i + 1) * M // chunks) for i in range(chunks)]
