@@ -133,3 +133,22 @@ def test_packed_checkpoint_and_calibration_host_errors():
         calibration.get_act_scales(torch.nn.Sequential(torch.nn.Linear(4, 4)), [torch.zeros(1, 4)])
     with pytest.raises(ValueError):
         calibration.collect_sort_keys(torch.nn.Linear(2, 2), [], "median")
+
+
+def test_fused_norm_falls_back_to_the_plain_norm_off_the_gpu_path():
+    """FusedNorm only hands out a lazy NormedRows for 16-bit CUDA rows; everything else gets the wrapped norm's output.
+    NormedRows carries the tensor attributes the attention / MLP blocks read and materialises the plain norm."""
+    import torch
+    from smoothquant_mixedprecision_b200 import fake_quant as fq
+    ln = torch.nn.LayerNorm(32)
+    x = torch.randn(2, 5, 32)
+    assert torch.equal(fq.FusedNorm(ln, "layer")(x), ln(x))
+    with pytest.raises(ValueError):
+        fq.FusedNorm(ln, "batch")
+    nr = fq.NormedRows(x, ln, "layer")
+    assert nr.shape == x.shape and nr.dim() == 3 and nr.size(-1) == 32 and nr.dtype == x.dtype and nr.device == x.device
+    assert nr.eps == ln.eps and torch.equal(nr.materialize(), ln(x)) and nr.materialize() is nr.materialize()
+    # a parent whose consumers are not packed fused layers keeps its norm
+    parent = torch.nn.Module()
+    parent.norm = ln
+    assert not fq.fuse_norm_(parent, "norm", [torch.nn.Linear(32, 8)], "layer") and parent.norm is ln
