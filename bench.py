@@ -157,7 +157,9 @@ def reference_arm(args):
     r = time_cpu(tokens, steps, warmup, n_layers)
     line = {"impl": "reference", "metric": METRIC, "value": r["tok_s"], "unit": "tokens/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["s_per_layer"] * LAYERS * 1e3 *
-            (args.tokens / tokens), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            (args.tokens / tokens), "higher_is_better": True,
+            # same job as the GPU arm at this N: one 32768-token batch (column-parallel headline) for N > 1
+            "scaling": "strong" if args.gpus > 1 and args.parallel != "dp" else "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
             "config": {"workload": "Llama-2-7B W4A4 linears g=128 5% salient, CPU fake-quant path", "tokens_per_step":
                        args.tokens, "group_size": GROUP, "salient_prop": SALIENT},
