@@ -471,13 +471,17 @@ class W4A4Linear(nn.Module):
             y = self._forward_fused(x, x2)
         else:
             y = self._forward_reference(x2, act_perm)
+        return self._finish(y, x2.dtype, shape if x.dim() == 3 else None, out_perm)
+
+    def _finish(self, y, dtype, shape3, out_perm=None):
+        """Everything behind the contraction: gather of a column-parallel layer, output quantiser, dtype, shape."""
         if self.tp_world > 1 and self.tp_gather_output:
             y = parallel.gather_columns(y, self.full_out_features, self.tp_group)
         if self.output_quant_name != "None":                           # fake_quant.py:309-316, on the full width
             y = self._quantize_output(y, out_perm)
-        if y.dtype != x2.dtype:
-            y = y.to(x2.dtype)
-        return y.view(shape[0], shape[1], -1) if x.dim() == 3 else y
+        if y.dtype != dtype:
+            y = y.to(dtype)
+        return y.view(*shape3[:-1], -1) if shape3 is not None else y
 
     def _norm_fusable(self):
         g = self.group_size
@@ -503,13 +507,7 @@ class W4A4Linear(nn.Module):
         if self._emits_blocked() and x.dim() == 2:
             return self._forward_fused(nx, x2, blocked_out=True, producer=producer)
         y = self._forward_fused(nx, x2, producer=producer)
-        if self.tp_world > 1 and self.tp_gather_output:
-            y = parallel.gather_columns(y, self.full_out_features, self.tp_group)
-        if self.output_quant_name != "None":
-            y = self._quantize_output(y, out_perm)
-        if y.dtype != x.dtype:
-            y = y.to(x.dtype)
-        return y.view(*x.shape[:-1], -1) if x.dim() == 3 else y
+        return self._finish(y, x.dtype, x.shape if x.dim() == 3 else None, out_perm)
 
     def _emits_blocked(self):
         return (self.tp_world > 1 and self.tp_gather_output and getattr(self, "tp_blocked_output", False)
@@ -529,7 +527,9 @@ class W4A4Linear(nn.Module):
               and self.in_features % 8 == 0 and self.quant_bits <= (8 if cdt == torch.float16 else 7))
         if not ok:
             return self.forward(xb.dense())
-        return self._forward_fused(xb, xb, blocked_out=self._emits_blocked())
+        if self._emits_blocked():
+            return self._forward_fused(xb, xb, blocked_out=True)
+        return self._finish(self._forward_fused(xb, xb), xb.dtype, None)
 
     # ---- column-parallel sharding over out_features; no reference counterpart
     @torch.no_grad()

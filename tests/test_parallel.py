@@ -198,6 +198,14 @@ def test_blocked_input_layer_matches_dense_input_layer():
             y = mod(x).clone()
             clear_act_cache()
             assert torch.equal(mod(P.BlockedColumns(buf, K)), y), (M, frac)
+        # an output-quantised layer (OPT q/k/v: N == K) behind a blocked input runs the output quantiser as usual
+        sq = torch.nn.Linear(K, K).half().cuda()
+        modq = W4A4Linear.from_float(sq, "per_group", "per_group", quantize_output=True, importance=imp,
+                                     salient_prop=0.05, group_size=g, mode="fused", sort_key=imp, int_fraction=1.0)
+        clear_act_cache()
+        yq = modq(x).clone()
+        clear_act_cache()
+        assert torch.equal(modq(P.BlockedColumns(buf, K)), yq), M
 
 
 def _nccl_pipeline_worker(rank, world, port):
