@@ -24,7 +24,7 @@ static MqOption g_options[] = {
     {"gemm_persistent", {0}}, {"quant_exact_div", {0}}, {"gemm_debug", {0}}, {"quant_force_generic", {0}},
     {"gemm_profile", {0}}, {"gemm_kernel", {0}}, {"gemm_pair", {0}}, {"gemm_magic_mma", {0}},
     {"quant_h2", {0}}, {"decode_bps", {0}}, {"decode_tpc", {0}}, {"decode_split", {0}},
-    {"sm_reserve", {0}},
+    {"sm_reserve", {0}}, {"pdl", {0}},
 };
 
 int mq_get_option(const char* name, int dflt) {

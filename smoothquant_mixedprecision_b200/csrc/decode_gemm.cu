@@ -226,6 +226,10 @@ decode_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
     tma_prefetch_desc(&map_as);
   }
   __syncthreads();
+  // barriers and descriptors are set up; everything below touches memory the previous kernel of the stream may have
+  // written (activation codes / scales) or may still be reading (y): wait for it here, not at the launch boundary
+  griddep_launch();
+  griddep_wait();
 
   if (warp == NW) {
     // ------------------------------------------------------------------ producer warp
@@ -529,21 +533,28 @@ int launch_decode_g(const CUtensorMap& ma, const CUtensorMap& mas, DecodeArgs p,
   p.tiles_per_cta = tpc;
   p.split = split;
   const int grid = (p.tiles + tpc - 1) / tpc * split;
-  if (split == 1) {
-    kern<<<grid, (NW + 1) * 32, smem, st>>>(ma, mas, p);
-  } else {
+  {
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3((unsigned)grid);
     cfg.blockDim = dim3((NW + 1) * 32);
     cfg.dynamicSmemBytes = smem;
     cfg.stream = st;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = (unsigned)split;
-    attr[0].val.clusterDim.y = 1;
-    attr[0].val.clusterDim.z = 1;
+    cudaLaunchAttribute attr[2];
+    int na = 0;
+    if (split > 1) {
+      attr[na].id = cudaLaunchAttributeClusterDimension;
+      attr[na].val.clusterDim.x = (unsigned)split;
+      attr[na].val.clusterDim.y = 1;
+      attr[na].val.clusterDim.z = 1;
+      ++na;
+    }
+    if (mq_get_option("pdl", 1) == 1) {   // overlap this kernel's launch + prologue with the tail of its predecessor
+      attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+      attr[na].val.programmaticStreamSerializationAllowed = 1;
+      ++na;
+    }
     cfg.attrs = attr;
-    cfg.numAttrs = 1;
+    cfg.numAttrs = na;
     MQ_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kern, ma, mas, p));
   }
   MQ_CHECK_CUDA(cudaGetLastError());

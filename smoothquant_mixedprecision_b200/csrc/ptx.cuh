@@ -138,6 +138,13 @@ __device__ __forceinline__ float4 lds_f32x4(uint32_t addr) {
 }
 
 // ------------------------------------------------------------------------------------------------ fences
+// Programmatic dependent launch: a kernel launched with cudaLaunchAttributeProgrammaticStreamSerialization may start
+// while its predecessor in the stream is still running; griddep_wait() blocks until the predecessor has completed and
+// its memory is visible (a no-op for an ordinary launch), griddep_launch() lets the successor's CTAs be scheduled as
+// soon as resources free up.
+__device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void griddep_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 __device__ __forceinline__ void fence_proxy_async_smem() {
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
 }

@@ -258,6 +258,8 @@ quant_rows_h2(const H2Args a) {
   using V2 = typename Pk<T>::V2;
   extern __shared__ __align__(128) unsigned char smem[];
   const QuantArgs& q = a.q;
+  griddep_launch();
+  griddep_wait();              // programmatic dependent launch: the input rows come from the previous kernel of the stream
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int K = (int)q.K, Kn = (int)q.Kn;
   const uint32_t pitch_b = (uint32_t)a.pitch * 2u;
@@ -572,7 +574,17 @@ int launch_h2(const H2Plan& p, cudaStream_t st) {
   if (grid > nblocks) grid = nblocks;
   auto go = [&](auto kern) -> int {
     MQ_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem));
-    kern<<<(unsigned)grid, kThreadsH2, p.smem, st>>>(a);
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((unsigned)grid);
+    cfg.blockDim = dim3(kThreadsH2);
+    cfg.dynamicSmemBytes = p.smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = mq_get_option("pdl", 1) == 1 ? 1 : 0;
+    MQ_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kern, a));
     MQ_CHECK_CUDA(cudaGetLastError());
     return MQ_OK;
   };

@@ -4,7 +4,9 @@ import json, os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 import torch
-from smoothquant_mixedprecision_b200 import ops
+from smoothquant_mixedprecision_b200 import ops, _lib
+if os.environ.get("MQ_PDL"):
+    _lib.set_option("pdl", int(os.environ["MQ_PDL"]))        # 2 = no programmatic dependent launch
 
 SHAPES = [("70b_q_o", 8192, 8192), ("70b_k_v", 1024, 8192), ("70b_gate_up", 28672, 8192), ("70b_down", 8192, 28672),
           ("7b_qkvo", 4096, 4096)]
