@@ -139,6 +139,10 @@ int mq_quant_rows_blocked(const void* x, int64_t R, int64_t K, int x_blocks, int
  *       MQ_NORM_RMS    y = rn(w * rn(x32 * rsqrt(mean(x32^2) + eps)))        (16-bit roundings as in transformers)
  *       MQ_NORM_LAYER  y = rn(((x32 - mean) * rsqrt(var + eps)) * w32 + b32)  (torch.nn.functional.layer_norm)
  *     then codes / scales / salient copy of y exactly as mq_quant_rows (bit-identical given the same y).
+ *     Row statistics are one-pass fp32 sums over all K columns (LayerNorm: var = E[x^2] - mean^2, clamped at 0): a row
+ *     whose |mean| exceeds ~1e3 x its standard deviation loses digits against torch's Welford update -- not a regime
+ *     transformer activations reach; y agrees with the torch norm to last-place units of the 16-bit type otherwise
+ *     (tests/test_ops_gpu.py::test_norm_quant_rows_is_norm_then_row_quantiser).
  *     out_y (nullable): the normalised rows [R, ld_y], for consumers outside the path and for the parity tests.
  *     16-bit dtypes, K % 8 == 0, K <= 16384, power-of-two group sizes 32..1024; otherwise MQ_ERR_UNSUPPORTED. */
 enum mq_norm_kind { MQ_NORM_RMS = 1, MQ_NORM_LAYER = 2 };
