@@ -152,3 +152,16 @@ def test_fused_norm_falls_back_to_the_plain_norm_off_the_gpu_path():
     parent = torch.nn.Module()
     parent.norm = ln
     assert not fq.fuse_norm_(parent, "norm", [torch.nn.Linear(32, 8)], "layer") and parent.norm is ln
+
+
+def test_integration_stub_matches_the_abi():
+    """The ctypes stub INTEGRATION.md shows a maintainer binds the same number of arguments as include/mq.h declares
+    (the stub went stale once when the workspace arguments were dropped)."""
+    from smoothquant_mixedprecision_b200 import _lib
+    text = open(os.path.join(ROOT, "INTEGRATION.md")).read()
+    found = re.findall(r"_lib\.(mq_\w+)\.argtypes = \[(.*?)\]", text, flags=re.S)
+    assert found, "no argtypes in the INTEGRATION.md stub"
+    for name, body in found:
+        n = len([a for a in body.replace("\n", " ").split(",") if a.strip()])
+        assert name in _lib.SIGNATURES and n == len(_lib.SIGNATURES[name][1]), (name, n, len(_lib.SIGNATURES[name][1]))
+    assert "mq_version() == 2" in text
